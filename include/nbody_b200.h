@@ -1,0 +1,142 @@
+/* include/nbody_b200.h — C ABI of libnbody_b200.so
+ *
+ * B200-native (sm_100a) replacement for ONE hot path of tusca99/N-body-simulation: the all-pairs gravity force
+ * evaluation (PAIRWISE, ADAPTIVE_MUTUAL) fused with the Velocity-Verlet / Euler step, i.e. what the reference runs
+ * behind config.json executionMode:"GPU". Plain C: pointers, integers and doubles only; no C++/torch types.
+ * Every function returns NB_OK (0) or an NB_ERR_* code; nb_last_error() gives the message for the calling thread.
+ * Nothing here ever exits the process, throws across the boundary, or falls back to a CPU implementation.
+ *
+ * Citations are file:line into the reference tree (simulator/...). INTEGRATION.md shows the reference-side binding.
+ *
+ * Particle layout is the reference's (core/Particles.hpp:9-16): AoS double4, posMass4[i] = (x,y,z,m),
+ * vel4[i] = (vx,vy,vz,0); units AU, Msun, yr; G = 39.47841760435743 (cuda/Constants.cuh:6).
+ */
+#ifndef NBODY_B200_H
+#define NBODY_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes -------------------------------------------------------------------------------------------- */
+#define NB_OK               0
+#define NB_ERR_INVALID      1   /* bad argument / call order                                  */
+#define NB_ERR_CUDA         2   /* CUDA runtime error (replaces gpuErrchk's exit(), cuda/CudaUtils.cu:5-10) */
+#define NB_ERR_NCCL         3
+#define NB_ERR_UNSUPPORTED  4   /* reference-only method (BARNES_HUT, PAIRWISE_AVX2_FP32, VISUALIZATION)     */
+#define NB_ERR_NO_DEVICE    5   /* replaces the std::runtime_error of cuda/SimulationKernels.cu:35-50         */
+
+/* ---- enums: numeric values are the reference's enum-class values ------------------------------------------------ */
+/* IntegrationMethod, core/System.hpp:15-18 */
+#define NB_INTEG_EULER            0
+#define NB_INTEG_VELOCITY_VERLET  1
+/* ForceMethod, core/Forces.hpp:40-46 */
+#define NB_FORCE_PAIRWISE            0
+#define NB_FORCE_PAIRWISE_AVX2_FP32  1   /* reference-only: NB_ERR_UNSUPPORTED */
+#define NB_FORCE_ADAPTIVE_MUTUAL     2
+#define NB_FORCE_BARNES_HUT          3   /* reference-only: NB_ERR_UNSUPPORTED */
+/* Arithmetic of the pair loop (new, optional; the reference GPU path is FP64 only) */
+#define NB_PREC_FP32   0   /* two-float (hi+lo) positions, FP32 pair math, FP64 accumulation across j-tiles; <=1e-5 */
+#define NB_PREC_FP64   1   /* FP64 pair math throughout; <=1e-12                                                    */
+
+typedef struct nb_ctx nb_ctx;
+
+/* Message of the last failing call on this thread ("" if none). Never NULL. */
+const char* nb_last_error(void);
+/* Library/ABI version and the SM architecture the kernels were built for (100). */
+int nb_abi_version(void);
+int nb_built_sm(void);
+/* Number of CUDA devices visible (0 when none); NB_ERR_NO_DEVICE semantics are left to the caller. */
+int nb_device_count(void);
+
+/* ---- context: device memory that persists across calls -----------------------------------------------------------
+ * Replaces the per-call cudaMalloc/cudaFree of cuda/BenchmarkKernels.cu:28-37,105-113 and
+ * cuda/SimulationKernels.cu:82-117,303-323. One context = one device = one host thread at a time. */
+int nb_create(nb_ctx** out, long n, int device, int precision);
+int nb_destroy(nb_ctx* ctx);
+
+/* Methods used by nb_compute_accel / nb_step. subtract_com != 0 removes the centre-of-mass velocity at the start of
+ * every step like the reference CPU integrators (core/System.cpp:45-57,392-400,438-446; the parity target);
+ * 0 reproduces the reference GPU drivers, which never do. Default after nb_create: VELOCITY_VERLET, PAIRWISE, 1. */
+int nb_set_methods(nb_ctx* ctx, int integration_method, int force_method, int subtract_com);
+
+/* Multi-GPU: this context owns the i-particles [n*rank/world, n*(rank+1)/world) (rounded to whole j-tiles) and
+ * all-gathers packed positions every step. No counterpart in the reference (single GPU).
+ * nb_partition_bounds is pure host arithmetic and needs no device. */
+int nb_partition_bounds(long n, int rank, int world, long* i_begin, long* i_count);
+int nb_comm_unique_id(void* id128);                               /* 128-byte ncclUniqueId, rank 0 creates it */
+int nb_comm_init(nb_ctx* ctx, const void* id128, int rank, int world);
+
+/* Host -> device of the whole system (cuda/BenchmarkKernels.cu:40-41). Buffers may be pinned or pageable. */
+int nb_upload(nb_ctx* ctx, const double* posMass4, const double* vel4);
+/* Device -> host of the final state (cuda/BenchmarkKernels.cu:101-102). Multi-GPU: only this rank's slice is
+ * written (rows i_begin .. i_begin+i_count of the full-size arrays). */
+int nb_download(nb_ctx* ctx, double* posMass4, double* vel4);
+
+/* a = F(x) for the current positions: the initial launchForceKernel of cuda/BenchmarkKernels.cu:68 /
+ * cuda/ForceKernels.cu:208-232. Must precede the first nb_step after an upload (nb_step does it if missing). */
+int nb_compute_accel(nb_ctx* ctx);
+/* Parity hook: copy accelerations to the host as n x double4 (ax,ay,az,0), the layout of the reference's d_accel
+ * (cuda/ForceKernels.cu:94). Multi-GPU: only this rank's rows are written. */
+int nb_get_accel(nb_ctx* ctx, double* accel4);
+
+/* nsteps x performGPUIntegrationStep (cuda/IntegrationKernels.cu:200-266). Asynchronous: returns after enqueueing;
+ * nb_sync / nb_download / nb_energy wait. */
+int nb_step(nb_ctx* ctx, double dt, int nsteps);
+int nb_sync(nb_ctx* ctx);
+
+/* out[0]=E, out[1]=kinetic, out[2]=potential with the semantics of System::computeTotalEnergy
+ * (core/System.cpp:60-85: unsoftened, every pair with r>0). O(N^2) in FP64. Single-GPU contexts only. */
+int nb_energy(nb_ctx* ctx, double out[3]);
+/* out = (sum m vx, sum m vy, sum m vz, sum m). */
+int nb_momentum(nb_ctx* ctx, double out[4]);
+/* Mean mass as computeAverageMass (core/Forces.cpp:85-95). */
+int nb_average_mass(nb_ctx* ctx, double* out);
+
+/* FILE_CSV sink (cuda/IntegrationKernels.cu:163-197; output/OutputData.hpp:14-31,387): writes one snapshot row.
+ * particleData6: n x (x,y,z,vx,vy,vz); systemData2: (time, energy) — energy is computed here; staticData2 (may be
+ * NULL): n x (id, mass). Host pointers. */
+int nb_snapshot(nb_ctx* ctx, double time, double* particleData6, double* systemData2, double* staticData2);
+
+/* Kernel launches enqueued by this context since creation (force + integrator + reduction kernels). */
+long nb_launch_count(nb_ctx* ctx);
+/* Duration in ms of the most recent force-kernel launch(es) of one force evaluation, measured with CUDA events on the
+ * context's stream (valid after nb_sync). */
+int nb_last_force_ms(nb_ctx* ctx, float* ms);
+/* Mean duration (ms) of the force evaluations since the last reset (at most the 64 most recent) and how many were
+ * averaged; waits for the stream. reset != 0 starts a new measurement window. */
+int nb_force_timing(nb_ctx* ctx, int reset, float* mean_ms, int* evals);
+/* CUDA-event stopwatch on the context's stream (torch.cuda.Event only sees torch's own streams):
+ * nb_timer_start records the start event; nb_timer_stop records the stop event, waits for it and returns the device
+ * time in ms of everything the context enqueued in between. */
+int nb_timer_start(nb_ctx* ctx);
+int nb_timer_stop(nb_ctx* ctx, float* ms);
+/* Tuning knobs (optional): "force_variant" 0 auto | 1 plain-load tiles | 2 bulk-copy (TMA) tiles; "j_splits" 0 auto. */
+int nb_set_option(nb_ctx* ctx, const char* key, long value);
+
+/* ---- whole-run entry points with HOST buffers: what the reference's host code binds ------------------------------ */
+/* runBenchmarkOnGPU(Particles&, IntegrationMethod, ForceMethod, dt, steps, BLOCK_SIZE)
+ * (cuda/BenchmarkKernels.cu:15-126, cuda/BenchmarkKernels.h:12-15). In place on posMass4/vel4. block_size is accepted
+ * and ignored (the launch configuration is fixed by the kernels). device<0: current device. */
+int nb_run_benchmark(long n, double* posMass4, double* vel4, int integration_method, int force_method,
+                     double dt, int steps, int block_size, int precision, int subtract_com, int device);
+/* runSimulationOnGPU(Particles&, method, forceMethod, dt, steps, stepFreq, OutputData&)
+ * (cuda/SimulationKernels.cu:22-286): snapshot 0 is the initial state, snapshot k is taken every step_freq steps;
+ * h_particleData [T][n][6], h_systemData [T][2], h_staticData [n][2] are the OutputData host arrays
+ * (output/OutputData.hpp:14-31); num_time_steps = T = steps/step_freq + 1 (core/System.cpp:107). */
+int nb_run_simulation(long n, double* posMass4, double* vel4, int integration_method, int force_method,
+                      double dt, int steps, int step_freq,
+                      double* h_particleData, double* h_systemData, double* h_staticData, long num_time_steps,
+                      int precision, int subtract_com, int device);
+
+/* ---- device-pointer entry points: the inner boundary of the reference drivers ------------------------------------ */
+/* launchForceKernel(method, blocks, blockSize, smem, stream, d_posMass, d_accel, avgMass, n)
+ * (cuda/ForceKernels.cu:208-232). d_posMass4 / d_accel4 are caller-owned device double4 arrays; the context provides
+ * the packed-tile scratch. avg_mass <= 0: computed on the device. stream: cudaStream_t (NULL = context stream). */
+int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, double* d_accel4,
+                    double avg_mass, long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBODY_B200_H */

@@ -1,0 +1,77 @@
+// nb_common.cuh — shared declarations of libnbody_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "nbody_b200.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ != 1000)
+#error "libnbody_b200 kernels are written for sm_100a (B200) only"
+#endif
+
+namespace nb {
+
+// Units and constants of the reference: cuda/Constants.cuh:6-8, core/Forces.cpp:14,305-306.
+constexpr double kG        = 39.47841760435743;
+constexpr double kEta      = 0.01;
+constexpr double kEpsMin   = 1e-4;
+constexpr double kR2Cut    = 1e-10;   // core/Forces.cpp:144,350 — pairs with r^2 < 1e-10 are skipped
+
+// ---- packed j-tile layout (FP32 mode) ----------------------------------------------------------------------------
+// Particles are grouped in tiles of kTJ. One tile is kNC contiguous rows of kTJ floats (8 KB), so a tile is ONE bulk
+// copy into shared memory and a float4 shared load yields the same component of four consecutive j-particles:
+//   row 0..2  xh yh zh   high parts of the position  (float)x
+//   row 3     gm         (float)(G * m)
+//   row 4..6  xl yl zl   low parts                   (float)(x - (double)xh)
+//   row 7     mq         (float)(m / (3 * mean mass))   (ADAPTIVE_MUTUAL only)
+constexpr int kTJ = 256;                 // j-particles per tile == threads per CTA
+constexpr int kNC = 8;                   // rows per tile
+constexpr int kTileFloats = kTJ * kNC;   // 2048 floats = 8192 bytes
+constexpr int kTileBytes  = kTileFloats * 4;
+constexpr int kAlign = 1024;             // particle counts are padded to a multiple of this (4 tiles)
+constexpr int kThreads = 256;
+
+struct ForceLaunch {          // one launch = i-tiles [it0, it0+nit) against the circular j-tile range
+    int it0, nit;             // i-tiles (units of kTJ particles); nit must be a multiple of R
+    int jt0, jcount;          // j-tiles jt0, jt0+1, ... (mod ntiles), jcount of them
+    int ntiles;               // tiles in the whole padded system
+    long npad;                // padded particle count (row stride of `part`)
+    int s0, S;                // this launch writes partial slots s0 .. s0+S-1
+};
+
+// Set thread-local error text; returns code.
+int fail(int code, const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define NB_CUDA(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return nb::cuda_fail(_e, #x, __FILE__, __LINE__); } while (0)
+
+// nb_force.cu
+int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, bool adaptive, int variant, cudaStream_t st);
+int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, bool adaptive, double avg_mass, cudaStream_t st);
+int launch_potential_fp64(const double4* pos, double* pot, long npad, int ntiles, cudaStream_t st);
+int force_regs_info(char* buf, int len);
+
+// nb_integrate.cu
+struct StepArrays {
+    double4* pos; double4* vel;     // master state, AoS like the reference (core/Particles.hpp:9-16)
+    double* acc;                    // current acceleration a = F(x), SoA [3][npad]
+    float* pk;                      // packed FP32 tiles (may be null in FP64 mode)
+    double* part;                   // force partials [S][3][npad]
+    double* red_part;               // per-block partial sums [nblocks][4] (sum m vx, m vy, m vz, m)
+    double* red;                    // final [4]
+    long npad; long n; long i0; long ni;   // owned slice [i0, i0+ni) (tile aligned), n real particles
+};
+int launch_pack(const StepArrays& A, long first, long count, double avg_mass, cudaStream_t st);
+int launch_drift(const StepArrays& A, int integ, double dt, bool subtract_com, double avg_mass, cudaStream_t st);
+int launch_finish(const StepArrays& A, int integ, bool kick, double dt, int S, cudaStream_t st);
+int launch_com_final(const StepArrays& A, cudaStream_t st);
+int launch_energy_reduce(const StepArrays& A, const double* pot, double* out3, cudaStream_t st);
+int launch_snapshot(const double4* pos, const double4* vel, long n, double* particleData6, double* staticData2, cudaStream_t st);
+int launch_accel_export(const double* acc, long npad, long first, long count, double4* out, cudaStream_t st);
+int launch_accel_import_sum(const double* part, int S, long npad, long n, double4* out, cudaStream_t st);
+int launch_mass_sum(const double4* pos, long n, double* red_part, double* red, cudaStream_t st);
+int launch_momentum(const double4* pos, const double4* vel, long first, long count, double* red_part, double* red, cudaStream_t st);
+
+} // namespace nb

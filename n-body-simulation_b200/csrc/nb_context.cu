@@ -1,0 +1,606 @@
+// nb_context.cu — the C ABI of include/nbody_b200.h: context, host<->device staging, step driver, multi-GPU exchange.
+//
+// Host-side counterpart of the reference GPU drivers runBenchmarkOnGPU (cuda/BenchmarkKernels.cu:15-126),
+// runSimulationOnGPU (cuda/SimulationKernels.cu:22-286) and performGPUIntegrationStep
+// (cuda/IntegrationKernels.cu:200-266), re-designed around a persistent context (no per-call cudaMalloc), error codes
+// instead of exit(), and an i-particle partition with an NCCL all-gather of the packed positions per step.
+#include "nb_common.cuh"
+
+#include <cstdarg>
+#include <cstdlib>
+#include <cstring>
+#include <dlfcn.h>
+#include <vector>
+
+namespace nb {
+
+static thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+    return code;
+}
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    const char* base = strrchr(file, '/'); base = base ? base + 1 : file;
+    snprintf(g_err, sizeof(g_err), "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), base, line, what);
+    cudaGetLastError();
+    return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? NB_ERR_NO_DEVICE : NB_ERR_CUDA;
+}
+
+// ---- NCCL, bound at run time (dlopen) so that the library loads on machines without it ------------------------------
+namespace nccl {
+typedef struct ncclComm* comm_t;
+struct unique_id { char internal[128]; };
+enum { kSuccess = 0 };
+enum { kFloat32 = 7, kFloat64 = 8, kSum = 0 };      // ncclDataType_t / ncclRedOp_t values (nccl.h)
+static void* lib = nullptr;
+static int (*GetUniqueId)(unique_id*) = nullptr;
+static int (*CommInitRank)(comm_t*, int, unique_id, int) = nullptr;
+static int (*CommDestroy)(comm_t) = nullptr;
+static int (*AllGather)(const void*, void*, size_t, int, comm_t, cudaStream_t) = nullptr;
+static int (*AllReduce)(const void*, void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+static const char* (*GetErrorString)(int) = nullptr;
+static int load() {
+    if (lib) return NB_OK;
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) { lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (lib) break; }
+    if (!lib) return fail(NB_ERR_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+#define NB_SYM(var, name) *(void**)(&var) = dlsym(lib, name); if (!var) return fail(NB_ERR_NCCL, "NCCL symbol %s missing", name)
+    NB_SYM(GetUniqueId, "ncclGetUniqueId"); NB_SYM(CommInitRank, "ncclCommInitRank"); NB_SYM(CommDestroy, "ncclCommDestroy");
+    NB_SYM(AllGather, "ncclAllGather"); NB_SYM(AllReduce, "ncclAllReduce"); NB_SYM(GetErrorString, "ncclGetErrorString");
+#undef NB_SYM
+    return NB_OK;
+}
+} // namespace nccl
+#define NB_NCCL(x) do { int _r = (x); if (_r != nccl::kSuccess) return nb::fail(NB_ERR_NCCL, "NCCL error %d (%s): %s", _r, nccl::GetErrorString ? nccl::GetErrorString(_r) : "?", #x); } while (0)
+
+static long round_up(long v, long m) { return (v + m - 1) / m * m; }
+
+} // namespace nb
+
+using namespace nb;
+
+struct nb_ctx {
+    int device = 0, precision = NB_PREC_FP32;
+    long n = 0, npad = 0; int ntiles = 0;
+    int integ = NB_INTEG_VELOCITY_VERLET, force = NB_FORCE_PAIRWISE, subtract_com = 1;
+    int rank = 0, world = 1; long i0 = 0, ni = 0;
+    cudaStream_t stream = nullptr, comm_stream = nullptr;
+    cudaEvent_t ev_packed = nullptr, ev_gathered = nullptr, tev0 = nullptr, tev1 = nullptr;
+    static constexpr int kRing = 64;
+    cudaEvent_t fev0[kRing] = {}, fev1[kRing] = {};   // ring of force-evaluation event pairs
+    long fev_count = 0;
+    double4 *pos = nullptr, *vel = nullptr, *tmp4 = nullptr;
+    double *acc = nullptr, *part = nullptr, *red_part = nullptr, *red = nullptr, *eout = nullptr;
+    float* pk = nullptr;
+    size_t part_bytes = 0;
+    double avg_mass = 0.0;
+    bool uploaded = false, have_accel = false, force_timed = false;
+    nccl::comm_t comm = nullptr;
+    long launches = 0;
+    int force_variant = 0, j_splits = 0;
+};
+
+namespace {
+
+StepArrays arrays(nb_ctx* c) {
+    StepArrays A;
+    A.pos = c->pos; A.vel = c->vel; A.acc = c->acc; A.pk = c->pk; A.part = c->part;
+    A.red_part = c->red_part; A.red = c->red; A.npad = c->npad; A.n = c->n; A.i0 = c->i0; A.ni = c->ni;
+    return A;
+}
+
+int use_device(nb_ctx* c) { NB_CUDA(cudaSetDevice(c->device)); return NB_OK; }
+
+int check_force_method(int force) {
+    if (force == NB_FORCE_PAIRWISE || force == NB_FORCE_ADAPTIVE_MUTUAL) return NB_OK;
+    if (force == NB_FORCE_BARNES_HUT || force == NB_FORCE_PAIRWISE_AVX2_FP32)
+        return fail(NB_ERR_UNSUPPORTED, "forceMethod %d is reference-only (BARNES_HUT / PAIRWISE_AVX2_FP32 are not part of the B200 hot path)", force);
+    return fail(NB_ERR_INVALID, "unknown forceMethod %d", force);
+}
+
+int splits_for(nb_ctx* c, int iblocks, int jcount) {
+    if (c->j_splits > 0) return c->j_splits < jcount ? c->j_splits : jcount;
+    // enough CTAs for >= 4 full waves of 148 SMs x 2 resident CTAs, so the tail wave costs little
+    const int target = 148 * 2 * 4;
+    int S = (target + iblocks - 1) / iblocks;
+    if (S > 32) S = 32;
+    if (S > jcount) S = jcount;
+    if (S < 1) S = 1;
+    return S;
+}
+
+int ensure_part(nb_ctx* c, int S_total) {
+    const size_t need = (size_t)S_total * 3 * (size_t)c->npad * sizeof(double);
+    if (need <= c->part_bytes) return NB_OK;
+    if (c->part) { NB_CUDA(cudaStreamSynchronize(c->stream)); NB_CUDA(cudaFree(c->part)); c->part = nullptr; c->part_bytes = 0; }
+    NB_CUDA(cudaMalloc(&c->part, need));
+    c->part_bytes = need;
+    return NB_OK;
+}
+
+int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const float* pk, double* part) {
+    const bool adaptive = (c->force == NB_FORCE_ADAPTIVE_MUTUAL);
+    int rc;
+    if (c->precision == NB_PREC_FP32) {
+        const int variant = c->force_variant == 0 ? 1 : c->force_variant;
+        rc = launch_force_fp32(pk, part, L, adaptive, variant, c->stream);
+    } else {
+        rc = launch_force_fp64(pos, part, L, adaptive, c->avg_mass, c->stream);
+    }
+    if (rc == NB_OK) c->launches++;
+    return rc;
+}
+
+// part[0..S) = partial sums of F(x) for the owned i-slice; returns S. Multi-GPU: the own j-slice is processed while the
+// all-gather of the remote slices is in flight on comm_stream.
+int eval_force(nb_ctx* c, int* S_out) {
+    const int R = c->precision == NB_PREC_FP32 ? 2 : 2;
+    const int nit = (int)(c->ni / kTJ), it0 = (int)(c->i0 / kTJ);
+    const int iblocks = nit / R;
+    ForceLaunch L; L.it0 = it0; L.nit = nit; L.ntiles = c->ntiles; L.npad = c->npad;
+    const int slot = (int)(c->fev_count % nb_ctx::kRing);
+    NB_CUDA(cudaEventRecord(c->fev0[slot], c->stream));
+    if (c->world == 1) {
+        L.jt0 = 0; L.jcount = c->ntiles; L.s0 = 0; L.S = splits_for(c, iblocks, L.jcount);
+        int rc = ensure_part(c, L.S); if (rc) return rc;
+        rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
+        *S_out = L.S;
+    } else {
+        const int St = splits_for(c, iblocks, c->ntiles);
+        int SA = St / c->world; if (SA < 1) SA = 1; if (SA > nit) SA = nit;
+        int SB = St - SA; if (SB < 1) SB = 1; if (SB > c->ntiles - nit) SB = c->ntiles - nit;
+        int rc = ensure_part(c, SA + SB); if (rc) return rc;
+        L.jt0 = it0; L.jcount = nit; L.s0 = 0; L.S = SA;
+        rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
+        NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+        L.jt0 = (it0 + nit) % c->ntiles; L.jcount = c->ntiles - nit; L.s0 = SA; L.S = SB;
+        rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
+        *S_out = SA + SB;
+    }
+    NB_CUDA(cudaEventRecord(c->fev1[slot], c->stream));
+    c->fev_count++;
+    c->force_timed = true;
+    return NB_OK;
+}
+
+// Multi-GPU exchange of the freshly packed own slice (in place inside the full packed array).
+int exchange_positions(nb_ctx* c) {
+    if (c->world == 1) return NB_OK;
+    NB_CUDA(cudaEventRecord(c->ev_packed, c->stream));
+    NB_CUDA(cudaStreamWaitEvent(c->comm_stream, c->ev_packed, 0));
+    if (c->precision == NB_PREC_FP32) {
+        const size_t count = (size_t)c->ni * kNC;                           // floats per rank
+        NB_NCCL(nccl::AllGather(c->pk + (size_t)c->i0 * kNC, c->pk, count, nccl::kFloat32, c->comm, c->comm_stream));
+    } else {
+        const size_t count = (size_t)c->ni * 4;                             // doubles per rank
+        NB_NCCL(nccl::AllGather((const double*)(c->pos + c->i0), (double*)c->pos, count, nccl::kFloat64, c->comm, c->comm_stream));
+    }
+    NB_CUDA(cudaEventRecord(c->ev_gathered, c->comm_stream));
+    return NB_OK;
+}
+
+int reduce_com(nb_ctx* c) {
+    StepArrays A = arrays(c);
+    int rc = launch_com_final(A, c->stream); if (rc) return rc;
+    c->launches++;
+    if (c->world > 1) NB_NCCL(nccl::AllReduce(c->red, c->red, 4, nccl::kFloat64, nccl::kSum, c->comm, c->stream));
+    return NB_OK;
+}
+
+int compute_accel(nb_ctx* c, bool kick, double dt) {
+    int S = 0;
+    int rc = eval_force(c, &S); if (rc) return rc;
+    StepArrays A = arrays(c);
+    rc = launch_finish(A, c->integ, kick, dt, S, c->stream); if (rc) return rc;
+    c->launches++;
+    return reduce_com(c);
+}
+
+} // namespace
+
+extern "C" {
+
+const char* nb_last_error(void) { return g_err; }
+int nb_abi_version(void) { return 1; }
+int nb_built_sm(void) { return 100; }
+
+int nb_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int nb_partition_bounds(long n, int rank, int world, long* i_begin, long* i_count) {
+    if (n <= 0 || world <= 0 || rank < 0 || rank >= world || !i_begin || !i_count)
+        return fail(NB_ERR_INVALID, "nb_partition_bounds: bad arguments n=%ld rank=%d world=%d", n, rank, world);
+    // Equal padded slices (the all-gather needs the same count on every rank); each a multiple of kAlign particles.
+    const long per = round_up(round_up(n, world) / world, kAlign);
+    long b = per * rank, e = b + per;
+    if (b > n) b = n;
+    if (e > n) e = n;
+    *i_begin = b; *i_count = e - b;
+    return NB_OK;
+}
+
+int nb_create(nb_ctx** out, long n, int device, int precision) {
+    if (!out) return fail(NB_ERR_INVALID, "nb_create: out is NULL");
+    *out = nullptr;
+    if (n <= 0 || n > (1L << 30)) return fail(NB_ERR_INVALID, "nb_create: n=%ld out of range", n);
+    if (precision != NB_PREC_FP32 && precision != NB_PREC_FP64) return fail(NB_ERR_INVALID, "nb_create: unknown precision %d", precision);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(NB_ERR_NO_DEVICE, "no CUDA device available (there is no CPU fallback)"); }
+    if (device < 0) { NB_CUDA(cudaGetDevice(&device)); }
+    if (device >= ndev) return fail(NB_ERR_INVALID, "nb_create: device %d of %d", device, ndev);
+    NB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop; NB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) return fail(NB_ERR_NO_DEVICE, "device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
+    nb_ctx* c = new nb_ctx();
+    c->device = device; c->precision = precision; c->n = n;
+    c->npad = round_up(n, kAlign); c->ntiles = (int)(c->npad / kTJ);
+    c->i0 = 0; c->ni = c->npad;
+    auto bail = [&](int rc) { nb_destroy(c); return rc; };
+#define NB_TRY(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return bail(cuda_fail(_e, #x, __FILE__, __LINE__)); } while (0)
+    NB_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    NB_TRY(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+    NB_TRY(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
+    NB_TRY(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
+    NB_TRY(cudaEventCreate(&c->tev0)); NB_TRY(cudaEventCreate(&c->tev1));
+    for (int k = 0; k < nb_ctx::kRing; ++k) { NB_TRY(cudaEventCreate(&c->fev0[k])); NB_TRY(cudaEventCreate(&c->fev1[k])); }
+    NB_TRY(cudaMalloc(&c->pos, (size_t)c->npad * sizeof(double4)));
+    NB_TRY(cudaMalloc(&c->vel, (size_t)c->npad * sizeof(double4)));
+    NB_TRY(cudaMalloc(&c->acc, (size_t)c->npad * 3 * sizeof(double)));
+    NB_TRY(cudaMalloc(&c->red_part, (size_t)(c->npad / kThreads) * 4 * sizeof(double)));
+    NB_TRY(cudaMalloc(&c->red, 16 * sizeof(double)));
+    NB_TRY(cudaMalloc(&c->eout, 16 * sizeof(double)));
+    if (precision == NB_PREC_FP32) NB_TRY(cudaMalloc(&c->pk, (size_t)c->npad * kNC * sizeof(float)));
+    NB_TRY(cudaMemsetAsync(c->pos, 0, (size_t)c->npad * sizeof(double4), c->stream));
+    NB_TRY(cudaMemsetAsync(c->vel, 0, (size_t)c->npad * sizeof(double4), c->stream));
+    NB_TRY(cudaMemsetAsync(c->acc, 0, (size_t)c->npad * 3 * sizeof(double), c->stream));
+    NB_TRY(cudaMemsetAsync(c->red, 0, 16 * sizeof(double), c->stream));
+#undef NB_TRY
+    *out = c;
+    return NB_OK;
+}
+
+int nb_destroy(nb_ctx* c) {
+    if (!c) return NB_OK;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
+    if (c->comm && nccl::CommDestroy) nccl::CommDestroy(c->comm);
+    cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->tmp4); cudaFree(c->acc); cudaFree(c->part);
+    cudaFree(c->red_part); cudaFree(c->red); cudaFree(c->eout); cudaFree(c->pk);
+    if (c->ev_packed) cudaEventDestroy(c->ev_packed);
+    if (c->ev_gathered) cudaEventDestroy(c->ev_gathered);
+    if (c->tev0) cudaEventDestroy(c->tev0);
+    if (c->tev1) cudaEventDestroy(c->tev1);
+    for (int k = 0; k < nb_ctx::kRing; ++k) { if (c->fev0[k]) cudaEventDestroy(c->fev0[k]); if (c->fev1[k]) cudaEventDestroy(c->fev1[k]); }
+    if (c->stream) cudaStreamDestroy(c->stream);
+    if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+    cudaGetLastError();
+    delete c;
+    return NB_OK;
+}
+
+int nb_set_methods(nb_ctx* c, int integ, int force, int subtract_com) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_set_methods: ctx is NULL");
+    if (integ != NB_INTEG_EULER && integ != NB_INTEG_VELOCITY_VERLET) return fail(NB_ERR_INVALID, "unknown integrationMethod %d", integ);
+    int rc = check_force_method(force); if (rc) return rc;
+    if (force != c->force) c->have_accel = false;
+    c->integ = integ; c->force = force; c->subtract_com = subtract_com ? 1 : 0;
+    return NB_OK;
+}
+
+int nb_set_option(nb_ctx* c, const char* key, long value) {
+    if (!c || !key) return fail(NB_ERR_INVALID, "nb_set_option: NULL argument");
+    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 2) return fail(NB_ERR_INVALID, "force_variant must be 0..2"); c->force_variant = (int)value; return NB_OK; }
+    if (!strcmp(key, "j_splits")) { if (value < 0 || value > 64) return fail(NB_ERR_INVALID, "j_splits must be 0..64"); c->j_splits = (int)value; return NB_OK; }
+    return fail(NB_ERR_INVALID, "nb_set_option: unknown key '%s'", key);
+}
+
+int nb_comm_unique_id(void* id128) {
+    if (!id128) return fail(NB_ERR_INVALID, "nb_comm_unique_id: NULL");
+    int rc = nccl::load(); if (rc) return rc;
+    nccl::unique_id id; memset(&id, 0, sizeof(id));
+    NB_NCCL(nccl::GetUniqueId(&id));
+    memcpy(id128, &id, 128);
+    return NB_OK;
+}
+
+int nb_comm_init(nb_ctx* c, const void* id128, int rank, int world) {
+    if (!c || !id128) return fail(NB_ERR_INVALID, "nb_comm_init: NULL argument");
+    if (world < 1 || rank < 0 || rank >= world) return fail(NB_ERR_INVALID, "nb_comm_init: rank %d of %d", rank, world);
+    if (c->uploaded) return fail(NB_ERR_INVALID, "nb_comm_init must precede nb_upload");
+    int rc = use_device(c); if (rc) return rc;
+    c->rank = rank; c->world = world;
+    if (world == 1) { c->i0 = 0; c->ni = c->npad; return NB_OK; }
+    // equal, tile-aligned slices; the padded system grows to world * per
+    const long per = round_up(round_up(c->n, world) / world, kAlign);
+    const long npad = per * world;
+    if (npad != c->npad) {
+        // re-allocate for the larger padding
+        const long n = c->n; const int dev = c->device, prec = c->precision;
+        const int integ = c->integ, force = c->force, sub = c->subtract_com, fv = c->force_variant, js = c->j_splits;
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->acc); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->part); cudaFree(c->tmp4);
+        c->pos = c->vel = c->tmp4 = nullptr; c->acc = c->red_part = c->part = nullptr; c->pk = nullptr; c->part_bytes = 0;
+        c->npad = npad; c->ntiles = (int)(npad / kTJ);
+        NB_CUDA(cudaMalloc(&c->pos, (size_t)npad * sizeof(double4)));
+        NB_CUDA(cudaMalloc(&c->vel, (size_t)npad * sizeof(double4)));
+        NB_CUDA(cudaMalloc(&c->acc, (size_t)npad * 3 * sizeof(double)));
+        NB_CUDA(cudaMalloc(&c->red_part, (size_t)(npad / kThreads) * 4 * sizeof(double)));
+        if (prec == NB_PREC_FP32) NB_CUDA(cudaMalloc(&c->pk, (size_t)npad * kNC * sizeof(float)));
+        NB_CUDA(cudaMemsetAsync(c->pos, 0, (size_t)npad * sizeof(double4), c->stream));
+        NB_CUDA(cudaMemsetAsync(c->vel, 0, (size_t)npad * sizeof(double4), c->stream));
+        NB_CUDA(cudaMemsetAsync(c->acc, 0, (size_t)npad * 3 * sizeof(double), c->stream));
+        (void)n; (void)dev; (void)integ; (void)force; (void)sub; (void)fv; (void)js;
+    }
+    c->i0 = per * rank; c->ni = per;
+    rc = nccl::load(); if (rc) return rc;
+    nccl::unique_id id; memcpy(&id, id128, 128);
+    NB_NCCL(nccl::CommInitRank(&c->comm, world, id, rank));
+    return NB_OK;
+}
+
+int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
+    if (!c || !posMass4 || !vel4) return fail(NB_ERR_INVALID, "nb_upload: NULL argument");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaMemcpyAsync(c->pos, posMass4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(c->vel, vel4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+    // computeAverageMass (core/Forces.cpp:85-95): serial sum in index order on the host, exactly as the reference.
+    double total = 0.0;
+    for (long i = 0; i < c->n; ++i) total += posMass4[4 * i + 3];
+    c->avg_mass = total / (double)c->n;
+    StepArrays A = arrays(c);
+    rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream); if (rc) return rc;
+    c->launches++;
+    c->uploaded = true; c->have_accel = false;
+    NB_CUDA(cudaStreamSynchronize(c->stream));      // the host buffers may be reused as soon as we return
+    return NB_OK;
+}
+
+int nb_download(nb_ctx* c, double* posMass4, double* vel4) {
+    if (!c || !posMass4 || !vel4) return fail(NB_ERR_INVALID, "nb_download: NULL argument");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_download before nb_upload");
+    int rc = use_device(c); if (rc) return rc;
+    long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;
+    if (e > b) {
+        NB_CUDA(cudaMemcpyAsync(posMass4 + 4 * b, c->pos + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(vel4 + 4 * b, c->vel + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+    }
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+int nb_compute_accel(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_compute_accel: ctx is NULL");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_compute_accel before nb_upload");
+    int rc = use_device(c); if (rc) return rc;
+    // every rank packed the whole system at upload, so no exchange is needed here; make the gather event "done"
+    if (c->world > 1) NB_CUDA(cudaEventRecord(c->ev_gathered, c->comm_stream));
+    rc = compute_accel(c, false, 0.0); if (rc) return rc;
+    c->have_accel = true;
+    return NB_OK;
+}
+
+int nb_get_accel(nb_ctx* c, double* accel4) {
+    if (!c || !accel4) return fail(NB_ERR_INVALID, "nb_get_accel: NULL argument");
+    if (!c->have_accel) return fail(NB_ERR_INVALID, "nb_get_accel before nb_compute_accel / nb_step");
+    int rc = use_device(c); if (rc) return rc;
+    if (!c->tmp4) NB_CUDA(cudaMalloc(&c->tmp4, (size_t)c->npad * sizeof(double4)));
+    long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;
+    rc = launch_accel_export(c->acc, c->npad, b, e - b, c->tmp4, c->stream); if (rc) return rc;
+    c->launches++;
+    if (e > b) NB_CUDA(cudaMemcpyAsync(accel4 + 4 * b, c->tmp4 + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+int nb_step(nb_ctx* c, double dt, int nsteps) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_step: ctx is NULL");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_step before nb_upload");
+    if (nsteps < 0) return fail(NB_ERR_INVALID, "nb_step: nsteps=%d", nsteps);
+    int rc = use_device(c); if (rc) return rc;
+    if (!c->have_accel) { rc = nb_compute_accel(c); if (rc) return rc; }
+    const bool vv = (c->integ == NB_INTEG_VELOCITY_VERLET);
+    for (int s = 0; s < nsteps; ++s) {
+        StepArrays A = arrays(c);
+        rc = launch_drift(A, c->integ, dt, c->subtract_com != 0, c->avg_mass, c->stream); if (rc) return rc;
+        c->launches++;
+        rc = exchange_positions(c); if (rc) return rc;
+        rc = compute_accel(c, vv, dt); if (rc) return rc;
+    }
+    return NB_OK;
+}
+
+int nb_sync(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_sync: ctx is NULL");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+int nb_energy(nb_ctx* c, double out[3]) {
+    if (!c || !out) return fail(NB_ERR_INVALID, "nb_energy: NULL argument");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_energy before nb_upload");
+    if (c->world > 1) return fail(NB_ERR_UNSUPPORTED, "nb_energy needs the whole system on one device (world=%d)", c->world);
+    int rc = use_device(c); if (rc) return rc;
+    if (!c->tmp4) NB_CUDA(cudaMalloc(&c->tmp4, (size_t)c->npad * sizeof(double4)));
+    double* pot = reinterpret_cast<double*>(c->tmp4);
+    rc = launch_potential_fp64(c->pos, pot, c->npad, c->ntiles, c->stream); if (rc) return rc;
+    StepArrays A = arrays(c);
+    rc = launch_energy_reduce(A, pot, c->eout, c->stream); if (rc) return rc;
+    c->launches += 4;
+    NB_CUDA(cudaMemcpyAsync(out, c->eout, 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+int nb_momentum(nb_ctx* c, double out[4]) {
+    if (!c || !out) return fail(NB_ERR_INVALID, "nb_momentum: NULL argument");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_momentum before nb_upload");
+    int rc = use_device(c); if (rc) return rc;
+    long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;
+    // red_part is shared with the step kernels: everything is on one stream, so this is ordered after them
+    rc = launch_momentum(c->pos, c->vel, b, e - b > 0 ? e - b : 1, c->red_part, c->eout + 8, c->stream); if (rc) return rc;
+    c->launches += 2;
+    if (c->world > 1) NB_NCCL(nccl::AllReduce(c->eout + 8, c->eout + 8, 4, nccl::kFloat64, nccl::kSum, c->comm, c->stream));
+    NB_CUDA(cudaMemcpyAsync(out, c->eout + 8, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+int nb_average_mass(nb_ctx* c, double* out) {
+    if (!c || !out) return fail(NB_ERR_INVALID, "nb_average_mass: NULL argument");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_average_mass before nb_upload");
+    *out = c->avg_mass;
+    return NB_OK;
+}
+
+int nb_snapshot(nb_ctx* c, double time, double* particleData6, double* systemData2, double* staticData2) {
+    if (!c || !particleData6 || !systemData2) return fail(NB_ERR_INVALID, "nb_snapshot: NULL argument");
+    if (c->world > 1) return fail(NB_ERR_UNSUPPORTED, "nb_snapshot needs the whole system on one device");
+    double e[3];
+    int rc = nb_energy(c, e); if (rc) return rc;
+    systemData2[0] = time; systemData2[1] = e[0];
+    // stage through device scratch: [n][6] then [n][2]
+    double* d6 = nullptr; double* d2 = nullptr;
+    NB_CUDA(cudaMalloc(&d6, (size_t)c->n * 8 * sizeof(double)));
+    d2 = d6 + (size_t)c->n * 6;
+    rc = launch_snapshot(c->pos, c->vel, c->n, d6, staticData2 ? d2 : nullptr, c->stream);
+    if (rc) { cudaFree(d6); return rc; }
+    c->launches++;
+    cudaError_t e1 = cudaMemcpyAsync(particleData6, d6, (size_t)c->n * 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+    cudaError_t e2 = staticData2 ? cudaMemcpyAsync(staticData2, d2, (size_t)c->n * 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream) : cudaSuccess;
+    cudaError_t e3 = cudaStreamSynchronize(c->stream);
+    cudaFree(d6);
+    NB_CUDA(e1); NB_CUDA(e2); NB_CUDA(e3);
+    return NB_OK;
+}
+
+long nb_launch_count(nb_ctx* c) { return c ? c->launches : 0; }
+
+int nb_last_force_ms(nb_ctx* c, float* ms) {
+    if (!c || !ms) return fail(NB_ERR_INVALID, "nb_last_force_ms: NULL argument");
+    if (!c->force_timed || c->fev_count == 0) return fail(NB_ERR_INVALID, "no force evaluation has run yet");
+    int rc = use_device(c); if (rc) return rc;
+    const int slot = (int)((c->fev_count - 1) % nb_ctx::kRing);
+    NB_CUDA(cudaEventSynchronize(c->fev1[slot]));
+    NB_CUDA(cudaEventElapsedTime(ms, c->fev0[slot], c->fev1[slot]));
+    return NB_OK;
+}
+
+int nb_force_timing(nb_ctx* c, int reset, float* mean_ms, int* evals) {
+    if (!c || !mean_ms || !evals) return fail(NB_ERR_INVALID, "nb_force_timing: NULL argument");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    const long cnt = c->fev_count < nb_ctx::kRing ? c->fev_count : nb_ctx::kRing;
+    double sum = 0.0;
+    for (long k = 0; k < cnt; ++k) {
+        const int slot = (int)((c->fev_count - 1 - k) % nb_ctx::kRing);
+        float ms = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&ms, c->fev0[slot], c->fev1[slot]));
+        sum += ms;
+    }
+    *mean_ms = cnt ? (float)(sum / (double)cnt) : 0.f;
+    *evals = (int)cnt;
+    if (reset) c->fev_count = 0;
+    return NB_OK;
+}
+
+int nb_timer_start(nb_ctx* c) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_timer_start: ctx is NULL");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaEventRecord(c->tev0, c->stream));
+    return NB_OK;
+}
+
+int nb_timer_stop(nb_ctx* c, float* ms) {
+    if (!c || !ms) return fail(NB_ERR_INVALID, "nb_timer_stop: NULL argument");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaEventRecord(c->tev1, c->stream));
+    NB_CUDA(cudaEventSynchronize(c->tev1));
+    NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+    NB_CUDA(cudaEventElapsedTime(ms, c->tev0, c->tev1));
+    return NB_OK;
+}
+
+int nb_run_benchmark(long n, double* posMass4, double* vel4, int integ, int force, double dt, int steps,
+                     int block_size, int precision, int subtract_com, int device) {
+    (void)block_size;
+    nb_ctx* c = nullptr;
+    int rc = nb_create(&c, n, device, precision); if (rc) return rc;
+    rc = nb_set_methods(c, integ, force, subtract_com);
+    if (!rc) rc = nb_upload(c, posMass4, vel4);
+    if (!rc) rc = nb_compute_accel(c);                 // cuda/BenchmarkKernels.cu:68
+    if (!rc) rc = nb_step(c, dt, steps);               // :75-88
+    if (!rc) rc = nb_download(c, posMass4, vel4);      // :101-102
+    nb_destroy(c);
+    return rc;
+}
+
+int nb_run_simulation(long n, double* posMass4, double* vel4, int integ, int force, double dt, int steps, int step_freq,
+                      double* h_particleData, double* h_systemData, double* h_staticData, long num_time_steps,
+                      int precision, int subtract_com, int device) {
+    if (!h_particleData || !h_systemData || !h_staticData) return fail(NB_ERR_INVALID, "nb_run_simulation: NULL output array");
+    if (step_freq < 1) step_freq = 1;
+    if (num_time_steps < 1) return fail(NB_ERR_INVALID, "nb_run_simulation: num_time_steps=%ld", num_time_steps);
+    nb_ctx* c = nullptr;
+    int rc = nb_create(&c, n, device, precision); if (rc) return rc;
+    rc = nb_set_methods(c, integ, force, subtract_com);
+    if (!rc) rc = nb_upload(c, posMass4, vel4);
+    if (!rc) rc = nb_compute_accel(c);                                                     // cuda/SimulationKernels.cu:167
+    if (!rc) rc = nb_snapshot(c, 0.0, h_particleData, h_systemData, h_staticData);          // :171-187 (snapshot 0)
+    int counter = 0; long tidx = 1;
+    for (int step = 1; step <= steps && !rc; ++step) {                                     // :193-228
+        rc = nb_step(c, dt, 1);
+        if (!rc && ++counter >= step_freq) {
+            if (tidx < num_time_steps)
+                rc = nb_snapshot(c, step * dt, h_particleData + (size_t)tidx * n * 6, h_systemData + tidx * 2, nullptr);
+            ++tidx; counter = 0;
+        }
+    }
+    if (!rc) rc = nb_download(c, posMass4, vel4);                                          // :246-249
+    nb_destroy(c);
+    return rc;
+}
+
+int nb_launch_force(nb_ctx* c, int force_method, const double* d_posMass4, double* d_accel4, double avg_mass, long n, void* stream) {
+    if (!c || !d_posMass4 || !d_accel4) return fail(NB_ERR_INVALID, "nb_launch_force: NULL argument");
+    if (n != c->n) return fail(NB_ERR_INVALID, "nb_launch_force: n=%ld but the context was created for %ld", n, c->n);
+    if (c->world > 1) return fail(NB_ERR_UNSUPPORTED, "nb_launch_force is single-device");
+    int rc = check_force_method(force_method); if (rc) return rc;
+    rc = use_device(c); if (rc) return rc;
+    cudaStream_t user = (cudaStream_t)stream;
+    // Order the context stream after the caller's stream and vice versa with events.
+    cudaEvent_t ev; NB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    if (user) { NB_CUDA(cudaEventRecord(ev, user)); NB_CUDA(cudaStreamWaitEvent(c->stream, ev, 0)); }
+    NB_CUDA(cudaMemcpyAsync(c->pos, d_posMass4, (size_t)n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+    const int saved_force = c->force;
+    c->force = force_method;
+    if (avg_mass > 0.0) c->avg_mass = avg_mass;
+    else {
+        rc = launch_mass_sum(c->pos, n, c->red_part, c->eout + 12, c->stream); if (rc) return rc;
+        double r4[4];
+        NB_CUDA(cudaMemcpyAsync(r4, c->eout + 12, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        c->avg_mass = r4[3] / (double)n;
+    }
+    StepArrays A = arrays(c);
+    rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream);
+    int S = 0;
+    if (!rc) rc = eval_force(c, &S);
+    if (!rc) rc = launch_accel_import_sum(c->part, S, c->npad, n, reinterpret_cast<double4*>(d_accel4), c->stream);
+    c->force = saved_force; c->have_accel = false; c->uploaded = true;
+    if (rc) { cudaEventDestroy(ev); return rc; }
+    c->launches += 2;
+    if (user) { NB_CUDA(cudaEventRecord(ev, c->stream)); NB_CUDA(cudaStreamWaitEvent(user, ev, 0)); }
+    else NB_CUDA(cudaStreamSynchronize(c->stream));
+    NB_CUDA(cudaEventDestroy(ev));
+    return NB_OK;
+}
+
+} // extern "C"

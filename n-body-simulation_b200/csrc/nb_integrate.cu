@@ -1,0 +1,288 @@
+// nb_integrate.cu — O(N) kernels around the force pass: packing, fused drift / kick, reductions, snapshots.
+//
+// Replaces velocityVerletPositionKernel / velocityVerletVelocityKernel / eulerIntegrationKernel and the
+// accel -> accelOld device copy of performGPUIntegrationStep (reference cuda/IntegrationKernels.cu:26-86,200-266),
+// computeTotalEnergyKernel's reduction (:89-160) and the snapshot kernels (:163-197). Unlike the reference GPU path
+// the centre-of-mass velocity is removed at the start of every step, as the CPU integrators do
+// (core/System.cpp:45-57,392-400,438-446) — the CPU path is the parity target.
+//
+// Per step (Velocity Verlet):   drift  : v -= v_cm ; x += v dt + a dt^2/2 ; re-pack x into FP32 hi/lo tiles
+//                               force  : part[s] = F(x) partial sums            (nb_force.cu)
+//                               finish : a' = sum_s part[s] ; v += (a + a') dt/2 ; a = a' ; block sums of m v
+//                               com    : v_cm numerator/denominator in fixed order (deterministic, no atomics)
+// All reductions are fixed-order so a run is bit-reproducible.
+#include "nb_common.cuh"
+
+namespace nb {
+namespace {
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// Block-wide sum of four values with warp shuffles; result valid in thread 0.
+__device__ __forceinline__ void block_sum4(double v[4], double* sh /* [4][8] */) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { v[c] = warp_sum(v[c]); if (lane == 0) sh[c * 8 + w] = v[c]; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { double s = 0.0; for (int k = 0; k < kThreads / 32; ++k) s += sh[c * 8 + k]; v[c] = s; }
+    }
+}
+
+__device__ __forceinline__ void pack_one(float* __restrict__ pk, long i, const double4 p, double inv3mbar) {
+    float* o = pk + (size_t)(i / kTJ) * kTileFloats + (i % kTJ);
+    const float xh = (float)p.x, yh = (float)p.y, zh = (float)p.z;
+    o[0 * kTJ] = xh; o[1 * kTJ] = yh; o[2 * kTJ] = zh;
+    o[3 * kTJ] = (float)(kG * p.w);
+    o[4 * kTJ] = (float)(p.x - (double)xh);
+    o[5 * kTJ] = (float)(p.y - (double)yh);
+    o[6 * kTJ] = (float)(p.z - (double)zh);
+    o[7 * kTJ] = (float)(p.w * inv3mbar);
+}
+
+__global__ void __launch_bounds__(kThreads)
+pack_kernel(const double4* __restrict__ pos, float* __restrict__ pk, long first, long count, double inv3mbar) {
+    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (k < count) pack_one(pk, first + k, pos[first + k], inv3mbar);
+}
+
+// drift: one thread per owned particle.
+template <int INTEG>
+__global__ void __launch_bounds__(kThreads)
+drift_kernel(StepArrays A, double dt, int subtract_com, double inv3mbar) {
+    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (k >= A.ni) return;
+    const long i = A.i0 + k;
+    if (i >= A.n) return;            // zero-mass pads stay at rest at the origin (packed once at upload)
+    double4 p = A.pos[i], v = A.vel[i];
+    if (subtract_com) {
+        const double M = A.red[3];
+        const double inv = M != 0.0 ? 1.0 / M : 0.0;
+        v.x -= A.red[0] * inv; v.y -= A.red[1] * inv; v.z -= A.red[2] * inv;
+    }
+    const double ax = A.acc[i], ay = A.acc[A.npad + i], az = A.acc[2 * A.npad + i];
+    if (INTEG == NB_INTEG_VELOCITY_VERLET) {
+        // cuda/IntegrationKernels.cu:36-38 ; core/System.cpp:463-465
+        p.x += v.x * dt + 0.5 * ax * (dt * dt);
+        p.y += v.y * dt + 0.5 * ay * (dt * dt);
+        p.z += v.z * dt + 0.5 * az * (dt * dt);
+        if (subtract_com) A.vel[i] = v;
+    } else {
+        // cuda/IntegrationKernels.cu:74-81 ; core/System.cpp:417-424: x uses the old v, then v += a dt
+        p.x += v.x * dt; p.y += v.y * dt; p.z += v.z * dt;
+        v.x += ax * dt; v.y += ay * dt; v.z += az * dt;
+        A.vel[i] = v;
+    }
+    A.pos[i] = p;
+    if (A.pk) pack_one(A.pk, i, p, inv3mbar);
+}
+
+// finish: reduce the force partials in slot order; VV kick; per-block sums of (m vx, m vy, m vz, m).
+template <bool KICK>
+__global__ void __launch_bounds__(kThreads)
+finish_kernel(StepArrays A, double dt, int S) {
+    __shared__ double sh[32];
+    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
+    double r[4] = {0.0, 0.0, 0.0, 0.0};
+    if (k < A.ni && A.i0 + k < A.n) {
+        const long i = A.i0 + k;
+        double ax = 0.0, ay = 0.0, az = 0.0;
+        for (int s = 0; s < S; ++s) {
+            const double* q = A.part + (size_t)s * 3 * A.npad;
+            ax += q[i]; ay += q[A.npad + i]; az += q[2 * A.npad + i];
+        }
+        double4 v = A.vel[i];
+        if (KICK) {
+            // cuda/IntegrationKernels.cu:55-57 ; core/System.cpp:484-486
+            v.x += 0.5 * (A.acc[i] + ax) * dt;
+            v.y += 0.5 * (A.acc[A.npad + i] + ay) * dt;
+            v.z += 0.5 * (A.acc[2 * A.npad + i] + az) * dt;
+            A.vel[i] = v;
+        }
+        A.acc[i] = ax; A.acc[A.npad + i] = ay; A.acc[2 * A.npad + i] = az;
+        const double m = A.pos[i].w;
+        r[0] = m * v.x; r[1] = m * v.y; r[2] = m * v.z; r[3] = m;
+    }
+    block_sum4(r, sh);
+    if (threadIdx.x == 0) {
+        double* o = A.red_part + (size_t)blockIdx.x * 4;
+        o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3];
+    }
+}
+
+// Single-CTA fixed-order sum of the per-block partials -> red[0..3].
+__global__ void __launch_bounds__(1024)
+reduce4_kernel(const double* __restrict__ red_part, long nblocks, double* __restrict__ red) {
+    __shared__ double sh[4][32];
+    double v[4] = {0.0, 0.0, 0.0, 0.0};
+    for (long b = threadIdx.x; b < nblocks; b += 1024) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) v[c] += red_part[b * 4 + c];
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) { v[c] = warp_sum(v[c]); if (lane == 0) sh[c][w] = v[c]; }
+    __syncthreads();
+    if (threadIdx.x < 4) { double s = 0.0; for (int k = 0; k < 32; ++k) s += sh[threadIdx.x][k]; red[threadIdx.x] = s; }
+}
+
+// Energy: block sums of (kinetic, m_i * pot_i, -, -) over all particles.
+__global__ void __launch_bounds__(kThreads)
+energy_partial_kernel(const double4* __restrict__ pos, const double4* __restrict__ vel, const double* __restrict__ pot,
+                      long n, double* __restrict__ red_part) {
+    __shared__ double sh[32];
+    const long i = (long)blockIdx.x * kThreads + threadIdx.x;
+    double r[4] = {0.0, 0.0, 0.0, 0.0};
+    if (i < n) {
+        const double4 p = pos[i], v = vel[i];
+        r[0] = 0.5 * p.w * (v.x * v.x + v.y * v.y + v.z * v.z);   // core/System.cpp:66-70
+        r[1] = p.w * pot[i];
+    }
+    block_sum4(r, sh);
+    if (threadIdx.x == 0) { double* o = red_part + (size_t)blockIdx.x * 4; o[0] = r[0]; o[1] = r[1]; o[2] = 0.0; o[3] = 0.0; }
+}
+__global__ void energy_final_kernel(const double* __restrict__ red, double* __restrict__ out3) {
+    const double kin = red[0], potl = -0.5 * kG * red[1];   // each unordered pair appears twice in sum_i m_i pot_i
+    out3[0] = kin + potl; out3[1] = kin; out3[2] = potl;
+}
+
+// Mass / momentum block sums straight from pos/vel (used after upload and by nb_momentum).
+__global__ void __launch_bounds__(kThreads)
+momentum_partial_kernel(const double4* __restrict__ pos, const double4* __restrict__ vel, long first, long count,
+                        double* __restrict__ red_part) {
+    __shared__ double sh[32];
+    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
+    double r[4] = {0.0, 0.0, 0.0, 0.0};
+    if (k < count) {
+        const double4 p = pos[first + k];
+        double4 v = make_double4(0, 0, 0, 0);
+        if (vel) v = vel[first + k];
+        r[0] = p.w * v.x; r[1] = p.w * v.y; r[2] = p.w * v.z; r[3] = p.w;
+    }
+    block_sum4(r, sh);
+    if (threadIdx.x == 0) { double* o = red_part + (size_t)blockIdx.x * 4; o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3]; }
+}
+
+// cuda/IntegrationKernels.cu:163-197: [i][6] = (x,y,z,vx,vy,vz); [i][2] = (id, mass)
+__global__ void __launch_bounds__(kThreads)
+snapshot_kernel(const double4* __restrict__ pos, const double4* __restrict__ vel, long n,
+                double* __restrict__ particleData6, double* __restrict__ staticData2) {
+    const long i = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n) return;
+    const double4 p = pos[i], v = vel[i];
+    double* o = particleData6 + (size_t)i * 6;
+    o[0] = p.x; o[1] = p.y; o[2] = p.z; o[3] = v.x; o[4] = v.y; o[5] = v.z;
+    if (staticData2) { staticData2[(size_t)i * 2] = (double)i; staticData2[(size_t)i * 2 + 1] = p.w; }
+}
+
+__global__ void __launch_bounds__(kThreads)
+accel_export_kernel(const double* __restrict__ acc, long npad, long first, long count, double4* __restrict__ out) {
+    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (k >= count) return;
+    const long i = first + k;
+    out[i] = make_double4(acc[i], acc[npad + i], acc[2 * npad + i], 0.0);   // cuda/ForceKernels.cu:94
+}
+__global__ void __launch_bounds__(kThreads)
+accel_sum_export_kernel(const double* __restrict__ part, int S, long npad, long n, double4* __restrict__ out) {
+    const long i = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n) return;
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (int s = 0; s < S; ++s) {
+        const double* q = part + (size_t)s * 3 * npad;
+        ax += q[i]; ay += q[npad + i]; az += q[2 * npad + i];
+    }
+    out[i] = make_double4(ax, ay, az, 0.0);
+}
+
+inline unsigned blocks_for(long count) { return (unsigned)((count + kThreads - 1) / kThreads); }
+
+} // namespace
+
+int launch_pack(const StepArrays& A, long first, long count, double avg_mass, cudaStream_t st) {
+    if (count <= 0 || !A.pk) return NB_OK;
+    const double inv3mbar = avg_mass > 0.0 ? 1.0 / (3.0 * avg_mass) : 0.0;
+    pack_kernel<<<blocks_for(count), kThreads, 0, st>>>(A.pos, A.pk, first, count, inv3mbar);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_drift(const StepArrays& A, int integ, double dt, bool subtract_com, double avg_mass, cudaStream_t st) {
+    if (A.ni <= 0) return NB_OK;
+    const double inv3mbar = avg_mass > 0.0 ? 1.0 / (3.0 * avg_mass) : 0.0;
+    if (integ == NB_INTEG_VELOCITY_VERLET)
+        drift_kernel<NB_INTEG_VELOCITY_VERLET><<<blocks_for(A.ni), kThreads, 0, st>>>(A, dt, subtract_com ? 1 : 0, inv3mbar);
+    else
+        drift_kernel<NB_INTEG_EULER><<<blocks_for(A.ni), kThreads, 0, st>>>(A, dt, subtract_com ? 1 : 0, inv3mbar);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_finish(const StepArrays& A, int integ, bool kick, double dt, int S, cudaStream_t st) {
+    if (A.ni <= 0) return NB_OK;
+    (void)integ;
+    if (kick) finish_kernel<true><<<blocks_for(A.ni), kThreads, 0, st>>>(A, dt, S);
+    else      finish_kernel<false><<<blocks_for(A.ni), kThreads, 0, st>>>(A, dt, S);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_com_final(const StepArrays& A, cudaStream_t st) {
+    reduce4_kernel<<<1, 1024, 0, st>>>(A.red_part, (long)blocks_for(A.ni), A.red);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_energy_reduce(const StepArrays& A, const double* pot, double* out3, cudaStream_t st) {
+    energy_partial_kernel<<<blocks_for(A.n), kThreads, 0, st>>>(A.pos, A.vel, pot, A.n, A.red_part);
+    NB_CUDA(cudaGetLastError());
+    reduce4_kernel<<<1, 1024, 0, st>>>(A.red_part, (long)blocks_for(A.n), out3 + 4);
+    NB_CUDA(cudaGetLastError());
+    energy_final_kernel<<<1, 1, 0, st>>>(out3 + 4, out3);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_snapshot(const double4* pos, const double4* vel, long n, double* particleData6, double* staticData2, cudaStream_t st) {
+    if (n <= 0) return NB_OK;
+    snapshot_kernel<<<blocks_for(n), kThreads, 0, st>>>(pos, vel, n, particleData6, staticData2);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_accel_export(const double* acc, long npad, long first, long count, double4* out, cudaStream_t st) {
+    if (count <= 0) return NB_OK;
+    accel_export_kernel<<<blocks_for(count), kThreads, 0, st>>>(acc, npad, first, count, out);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_accel_import_sum(const double* part, int S, long npad, long n, double4* out, cudaStream_t st) {
+    if (n <= 0) return NB_OK;
+    accel_sum_export_kernel<<<blocks_for(n), kThreads, 0, st>>>(part, S, npad, n, out);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+// red[0..3] = (sum m vx, sum m vy, sum m vz, sum m) over [first, first+count)
+int launch_mass_sum(const double4* pos, long n, double* red_part, double* red, cudaStream_t st) {
+    momentum_partial_kernel<<<blocks_for(n), kThreads, 0, st>>>(pos, nullptr, 0, n, red_part);
+    NB_CUDA(cudaGetLastError());
+    reduce4_kernel<<<1, 1024, 0, st>>>(red_part, (long)blocks_for(n), red);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+int launch_momentum(const double4* pos, const double4* vel, long first, long count, double* red_part, double* red, cudaStream_t st) {
+    momentum_partial_kernel<<<blocks_for(count), kThreads, 0, st>>>(pos, vel, first, count, red_part);
+    NB_CUDA(cudaGetLastError());
+    reduce4_kernel<<<1, 1024, 0, st>>>(red_part, (long)blocks_for(count), red);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+} // namespace nb

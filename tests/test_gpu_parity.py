@@ -1,0 +1,241 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on identical inputs.
+
+Tolerances (BASELINE.json north_star): per-particle acceleration relative error <= 1e-5 in FP32 mode and <= 1e-12 in
+FP64 mode; energy / momentum drift within 1% of the reference's drift."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import nbtest
+from nbtest import ADAPTIVE, EULER, FP32, FP64, PAIRWISE, VV
+
+pytestmark = pytest.mark.gpu
+
+TOL = {FP32: 1e-5, FP64: 1e-12}
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_vectors.npz"))
+
+
+def gpu_accel(lib, pm, v, force, prec, **opts):
+    with lib.context(pm.shape[0], prec) as ctx:
+        for k, val in opts.items():
+            ctx.set_option(k, val)
+        ctx.set_methods(VV, force, 1)
+        ctx.upload(pm, v)
+        ctx.compute_accel()
+        return ctx.accel()
+
+
+DATASETS = {
+    "three_body": lambda: (GOLD["kat1_pm"].copy(), np.zeros((3, 4))),
+    "sistema": lambda: (GOLD["sis_pm"].copy(), GOLD["sis_v"].copy()),
+    "cutoff": lambda: (GOLD["cut_pm"].copy(), np.zeros((5, 4))),
+    "single": lambda: (np.array([[1.0, 2.0, 3.0, 4.0]]), np.zeros((1, 4))),
+    "random_333": lambda: (GOLD["rnd333_pm"].copy(), GOLD["rnd333_v"].copy()),
+    "random_4096": lambda: nbtest.gen_random(4096, seed=42),
+    "random_5000_ragged": lambda: nbtest.gen_random(5000, seed=43),
+    "spiral_16384": lambda: nbtest.gen_spiral(16384, seed=42),
+    "galaxy_planets_3001": lambda: nbtest.gen_galaxy(1000, 2, seed=42),
+}
+
+
+@pytest.mark.parametrize("prec", [FP32, FP64], ids=["fp32", "fp64"])
+@pytest.mark.parametrize("force", [PAIRWISE, ADAPTIVE], ids=["pairwise", "adaptive"])
+@pytest.mark.parametrize("name", list(DATASETS))
+def test_acceleration_parity(lib, oracle, name, force, prec):
+    pm, v = DATASETS[name]()
+    a = gpu_accel(lib, pm, v, force, prec)
+    ref = oracle.forces(pm, force)
+    assert np.all(np.isfinite(a))
+    assert np.all(a[:, 3] == 0.0)
+    err = nbtest.rel_err(a, ref)
+    assert err.max() <= TOL[prec], f"{name}: max rel err {err.max():.3e} (median {np.median(err):.3e})"
+
+
+@pytest.mark.parametrize("key,force", [("pairwise", PAIRWISE), ("adaptive", ADAPTIVE)])
+@pytest.mark.parametrize("ds", ["kat1", "rnd96", "rnd333", "cut", "gal"])
+def test_golden_vectors_from_reference(lib, ds, key, force):
+    """Against the committed outputs of the reference's own code (no oracle in the loop)."""
+    pm = GOLD[f"{ds}_pm"].copy()
+    for prec in (FP32, FP64):
+        a = gpu_accel(lib, pm, np.zeros_like(pm), force, prec)
+        err = nbtest.rel_err(a, GOLD[f"{ds}_{key}"])
+        assert err.max() <= TOL[prec], (ds, key, prec, err.max())
+
+
+@pytest.mark.parametrize("force", [PAIRWISE, ADAPTIVE], ids=["pairwise", "adaptive"])
+def test_tile_staging_variants_agree_bitwise(lib, force):
+    """Plain-load tiles (variant 1) and bulk-copy/mbarrier tiles (variant 2) run the same arithmetic."""
+    pm, v = nbtest.gen_spiral(20000, seed=1)
+    a1 = gpu_accel(lib, pm, v, force, FP32, force_variant=1)
+    a2 = gpu_accel(lib, pm, v, force, FP32, force_variant=2)
+    assert np.array_equal(a1, a2)
+
+
+@pytest.mark.parametrize("prec", [FP32, FP64], ids=["fp32", "fp64"])
+def test_j_splits_do_not_change_the_answer(lib, oracle, prec):
+    pm, v = nbtest.gen_random(6000, seed=5)
+    ref = oracle.forces(pm, PAIRWISE)
+    for S in (1, 3, 24):
+        a = gpu_accel(lib, pm, v, PAIRWISE, prec, j_splits=S)
+        assert nbtest.rel_err(a, ref).max() <= TOL[prec]
+
+
+def test_run_is_bit_reproducible(lib):
+    pm, v = nbtest.gen_spiral(8192, seed=2)
+    r1 = lib.run_benchmark(pm, v, VV, PAIRWISE, 0.04, 3, precision=FP32)
+    r2 = lib.run_benchmark(pm, v, VV, PAIRWISE, 0.04, 3, precision=FP32)
+    assert np.array_equal(r1[0], r2[0]) and np.array_equal(r1[1], r2[1])
+
+
+@pytest.mark.parametrize("prec", [FP32, FP64], ids=["fp32", "fp64"])
+@pytest.mark.parametrize("integ,force", [(VV, PAIRWISE), (VV, ADAPTIVE), (EULER, PAIRWISE), (EULER, ADAPTIVE)],
+                         ids=["vv-pairwise", "vv-adaptive", "euler-pairwise", "euler-adaptive"])
+def test_step_parity_with_cpu_integrators(lib, oracle, integ, force, prec):
+    """nb_run_benchmark (= runBenchmarkOnGPU) against System::runBenchmark in CPU mode, 20 steps."""
+    pm, v = nbtest.gen_random(2000, seed=9)
+    p_ref, v_ref = oracle.step(pm, v, integ, force, 0.01, 20)
+    p, w = lib.run_benchmark(pm, v, integ, force, 0.01, 20, precision=prec)
+    tol = 1e-6 if prec == FP32 else 1e-10
+    assert np.abs(p[:, :3] - p_ref[:, :3]).max() <= tol * 50.0        # box half-width 50 AU
+    assert np.abs(w[:, :3] - v_ref[:, :3]).max() <= tol * 10.0
+    assert np.array_equal(p[:, 3], pm[:, 3])                          # masses untouched
+
+
+def test_golden_sistema_50_steps(lib):
+    pm, v = GOLD["sis_pm"].copy(), GOLD["sis_v"].copy()
+    for name, integ, force in (("vv_pw", VV, PAIRWISE), ("eu_ad", EULER, ADAPTIVE)):
+        p, w = lib.run_benchmark(pm, v, integ, force, 0.04, 50, precision=FP64)
+        np.testing.assert_allclose(p, GOLD[f"sis_pm50_{name}"], rtol=0, atol=1e-7)
+        np.testing.assert_allclose(w, GOLD[f"sis_v50_{name}"], rtol=0, atol=1e-6)
+
+
+@pytest.mark.parametrize("prec", [FP32, FP64], ids=["fp32", "fp64"])
+def test_energy_and_momentum_drift_match_reference(lib, oracle, prec):
+    """KAT-2: sistema.dat, dt = 0.04, 2500 VV steps: the drift Delta E is within 1% of the CPU path's drift."""
+    pm, v = GOLD["sis_pm"].copy(), GOLD["sis_v"].copy()
+    e0 = float(GOLD["sis_E0"])
+    with lib.context(25, prec) as ctx:
+        ctx.set_methods(VV, PAIRWISE, 1)
+        ctx.upload(pm, v)
+        eg0 = ctx.energy()[0]
+        ctx.step(0.04, 2500)
+        eg1 = ctx.energy()[0]
+        mom = ctx.momentum()
+    assert abs(eg0 - e0) <= 1e-13 * abs(e0)
+    d_ref = float(GOLD["sis_E2500_vv_pw"]) - e0
+    d_gpu = eg1 - eg0
+    assert abs(d_gpu - d_ref) <= 0.01 * abs(d_ref), (d_gpu, d_ref)
+    assert np.linalg.norm(mom[:3]) < 1e-12            # COM velocity removed every step (reference: 1.4e-18)
+    assert mom[3] == pytest.approx(pm[:, 3].sum(), rel=1e-14)
+
+
+def test_drift_on_spiral_matches_cpu(lib, oracle):
+    pm, v = nbtest.gen_spiral(3000, seed=4)
+    e0 = oracle.energy(pm, v)
+    p_ref, v_ref = oracle.step(pm, v, VV, PAIRWISE, 0.04, 10)
+    d_ref = oracle.energy(p_ref, v_ref) - e0
+    for prec in (FP32, FP64):
+        with lib.context(3000, prec) as ctx:
+            ctx.set_methods(VV, PAIRWISE, 1)
+            ctx.upload(pm, v)
+            eg0 = ctx.energy()[0]
+            ctx.step(0.04, 10)
+            eg1 = ctx.energy()[0]
+        assert abs(eg0 - e0) <= 1e-12 * abs(e0)
+        assert abs((eg1 - eg0) - d_ref) <= 0.01 * abs(d_ref), (prec, eg1 - eg0, d_ref)
+
+
+def test_subtract_com_flag_reproduces_reference_gpu_semantics(lib, oracle):
+    """subtract_com=0 is the reference GPU driver (no COM removal): momentum is conserved, not zeroed."""
+    pm, v = nbtest.gen_random(1500, seed=6)
+    v[:, 0] += 0.3                                    # net drift
+    p0 = oracle.momentum(pm, v)
+    with lib.context(1500, FP64) as ctx:
+        ctx.set_methods(VV, PAIRWISE, 0)
+        ctx.upload(pm, v)
+        ctx.step(0.01, 5)
+        m = ctx.momentum()
+    np.testing.assert_allclose(m[:3], p0, rtol=1e-9)
+    with lib.context(1500, FP64) as ctx:
+        ctx.set_methods(VV, PAIRWISE, 1)
+        ctx.upload(pm, v)
+        ctx.step(0.01, 5)
+        m = ctx.momentum()
+    assert np.linalg.norm(m[:3]) < 1e-12 * np.linalg.norm(p0) + 1e-18
+
+
+def test_run_simulation_snapshots(lib, oracle):
+    """nb_run_simulation (= runSimulationOnGPU): snapshot layout, times, energies, static data."""
+    pm, v = nbtest.gen_random(300, seed=8)
+    p, w, pdata, sdata, stat = lib.run_simulation(pm, v, VV, PAIRWISE, 0.01, 10, 5, precision=FP64)
+    assert pdata.shape == (3, 300, 6)
+    np.testing.assert_array_equal(pdata[0, :, :3], pm[:, :3])
+    np.testing.assert_array_equal(pdata[0, :, 3:], v[:, :3])
+    np.testing.assert_array_equal(stat[:, 0], np.arange(300))
+    np.testing.assert_array_equal(stat[:, 1], pm[:, 3])
+    np.testing.assert_allclose(sdata[:, 0], [0.0, 0.05, 0.10])
+    assert sdata[0, 1] == pytest.approx(oracle.energy(pm, v), rel=1e-12)
+    p5, v5 = oracle.step(pm, v, VV, PAIRWISE, 0.01, 5)
+    np.testing.assert_allclose(pdata[1, :, :3], p5[:, :3], atol=1e-9)
+    assert sdata[1, 1] == pytest.approx(oracle.energy(p5, v5), rel=1e-9)
+    np.testing.assert_array_equal(pdata[2, :, :3], p[:, :3])
+
+
+def test_unsupported_methods_fail_cleanly(lib):
+    pm, v = nbtest.gen_random(64)
+    for force in (nbtest.BARNES_HUT, nbtest.AVX2):
+        with pytest.raises(nbtest.NbError) as ei:
+            lib.run_benchmark(pm, v, VV, force, 0.01, 1)
+        assert ei.value.code == 4 and "reference-only" in str(ei.value)
+    with lib.context(64) as ctx:
+        with pytest.raises(nbtest.NbError):
+            ctx.step(0.01, 1)                        # before upload
+        with pytest.raises(nbtest.NbError):
+            ctx.set_methods(5, PAIRWISE, 1)
+
+
+def test_launch_force_on_caller_device_arrays(lib, oracle):
+    """nb_launch_force (= launchForceKernel): caller-owned device double4 arrays, caller's stream."""
+    import torch
+    pm, v = nbtest.gen_spiral(5000, seed=3)
+    d_pos = torch.from_numpy(pm).cuda()
+    d_acc = torch.zeros_like(d_pos)
+    stream = torch.cuda.Stream()
+    with lib.context(5000, FP32) as ctx:
+        with torch.cuda.stream(stream):
+            for force in (PAIRWISE, ADAPTIVE):
+                lib.check(lib.l.nb_launch_force(ctx.h, force, C.c_void_p(d_pos.data_ptr()), C.c_void_p(d_acc.data_ptr()),
+                                                -1.0, 5000, C.c_void_p(stream.cuda_stream)))
+                stream.synchronize()
+                a = d_acc.cpu().numpy()
+                assert nbtest.rel_err(a, oracle.forces(pm, force)).max() <= 1e-5
+
+
+# ---- BASELINE.json sizes: size-independent properties + sampled-subset arbiter --------------------------------------
+@pytest.mark.parametrize("n,gen,force,prec", [
+    (65536, "random", PAIRWISE, FP32), (262144, "galaxy", ADAPTIVE, FP32), (262144, "galaxy", ADAPTIVE, FP64),
+    (1048576, "spiral", PAIRWISE, FP32)], ids=["C2-random-65536", "C4-galaxy-262144-fp32", "C4-galaxy-262144-fp64",
+                                              "C3-spiral-1M"])
+def test_full_size_configs(lib, oracle, n, gen, force, prec):
+    if gen == "random":
+        pm, v = nbtest.gen_random(n, seed=42)
+    elif gen == "spiral":
+        pm, v = nbtest.gen_spiral(n, seed=42)
+    else:
+        pm, v = nbtest.gen_galaxy((n - 1) // 3, 2, seed=42)
+        assert pm.shape[0] == n
+    a = gpu_accel(lib, pm, v, force, prec)
+    assert np.all(np.isfinite(a))
+    # sampled-subset arbiter: 192 i-particles against all j in long double on the CPU
+    idx = np.random.default_rng(0).choice(n, 192, replace=False)
+    idx[:3] = [0, 1, n - 1]
+    ref = oracle.forces_subset(pm, force, idx)
+    err = nbtest.rel_err(a[idx], ref)
+    assert err.max() <= TOL[prec], f"max {err.max():.3e} median {np.median(err):.3e}"
+    # Newton's third law (PAIRWISE is antisymmetric): sum m_i a_i = 0 up to round-off of the big terms
+    if force == PAIRWISE:
+        tot = (pm[:, 3:4] * a[:, :3]).sum(0)
+        scale = np.abs(pm[:, 3:4] * a[:, :3]).sum(0)
+        assert np.all(np.abs(tot) <= 2e-6 * scale)

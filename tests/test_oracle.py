@@ -1,0 +1,167 @@
+"""CPU tests: pin the plain-C oracle (oracle/nbody_oracle.c) against the known-answer vectors produced from the
+reference's own code (tests/golden/ref_vectors.npz) and, when present, against oracle/_ref directly."""
+import os
+
+import numpy as np
+import pytest
+
+import nbtest
+from nbtest import ADAPTIVE, EULER, PAIRWISE, VV
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_vectors.npz"))
+
+# KAT-1 literals as printed in SURVEY.md §8c (independent of the .npz)
+KAT1_PW = np.array([[1.184352528130723e-04, 1.460000651048721e-03, 0.0],
+                    [-3.947868348867519e+01, 1.382598452356394e-03, 0.0],
+                    [7.976529532825347e-07, -1.460004798844078e+00, 0.0]])
+KAT1_AD = np.array([[1.184175015762244e-04, 1.459781678760335e-03, 0.0],
+                    [-3.947276640932652e+01, 1.382596375703948e-03, 0.0],
+                    [7.976517552138162e-07, -1.459785826549462e+00, 0.0]])
+
+
+def test_kat1_three_body(oracle):
+    pm = GOLD["kat1_pm"]
+    np.testing.assert_allclose(oracle.forces(pm, PAIRWISE), KAT1_PW, rtol=1e-14, atol=1e-300)
+    np.testing.assert_allclose(oracle.forces(pm, ADAPTIVE), KAT1_AD, rtol=1e-14, atol=1e-300)
+    np.testing.assert_allclose(GOLD["kat1_pairwise"], KAT1_PW, rtol=1e-14, atol=1e-300)
+    # |a_1| ~ G * 1 / 1^2
+    assert abs(np.linalg.norm(oracle.forces(pm, PAIRWISE)[1]) - nbtest.G) < 1e-3
+
+
+def test_sistema_loader_matches_reference():
+    pm, v = nbtest.load_sistema()
+    assert pm.shape == (25, 4)
+    np.testing.assert_allclose(pm, GOLD["sis_pm"], rtol=1e-15)
+    np.testing.assert_allclose(v, GOLD["sis_v"], rtol=1e-15)
+    np.testing.assert_allclose(pm[0], [2.245543e-03, -4.396472e-03, -6.053404e-05, 9.997486e-01], rtol=1e-6)
+
+
+def test_kat2_sistema_energy(oracle):
+    pm, v = GOLD["sis_pm"], GOLD["sis_v"]
+    e0 = oracle.energy(pm, v)
+    assert abs(e0 - (-4.436930341056258e-03)) < 1e-17
+    assert abs(e0 - float(GOLD["sis_E0"])) < 1e-17
+    assert abs(np.linalg.norm(oracle.momentum(pm, v)) - 2.658896e-08) < 1e-13
+
+
+@pytest.mark.parametrize("name,integ,force,e_survey", [
+    ("vv_pw", VV, PAIRWISE, -4.202326813391120e-03), ("vv_ad", VV, ADAPTIVE, -4.203119128559666e-03),
+    ("eu_pw", EULER, PAIRWISE, -1.415610092240299e-03), ("eu_ad", EULER, ADAPTIVE, -1.420347794518450e-03)])
+def test_kat2_sistema_runs(oracle, name, integ, force, e_survey):
+    pm, v = GOLD["sis_pm"], GOLD["sis_v"]
+    # 50 steps: trajectories still agree closely (the under-resolved Earth-Moon pair amplifies the round-off
+    # difference between -ffast-math and IEEE evaluation by ~1e6 over 50 steps)
+    p50, v50 = oracle.step(pm, v, integ, force, 0.04, 50)
+    np.testing.assert_allclose(p50, GOLD[f"sis_pm50_{name}"], rtol=0, atol=1e-7)
+    np.testing.assert_allclose(v50, GOLD[f"sis_v50_{name}"], rtol=0, atol=1e-6)
+    assert abs(oracle.energy(p50, v50) - float(GOLD[f"sis_E50_{name}"])) < 1e-10 * abs(float(GOLD[f"sis_E50_{name}"]))
+    # 2500 steps (config.json defaults): chaotic (Earth-Moon at dt = 14.6 d), so compare the energy only
+    p, w = oracle.step(pm, v, integ, force, 0.04, 2500)
+    e = oracle.energy(p, w)
+    assert abs(e - float(GOLD[f"sis_E2500_{name}"])) < 2e-9 * abs(e)
+    assert abs(e - e_survey) < 2e-9 * abs(e)
+    if integ == VV:
+        assert np.linalg.norm(oracle.momentum(p, w)) < 1e-15     # COM velocity is removed every step
+
+
+@pytest.mark.parametrize("n", [96, 333])
+def test_golden_random(oracle, n):
+    pm, v = GOLD[f"rnd{n}_pm"], GOLD[f"rnd{n}_v"]
+    for key, method in (("pairwise", PAIRWISE), ("adaptive", ADAPTIVE)):
+        err = nbtest.rel_err(oracle.forces(pm, method), GOLD[f"rnd{n}_{key}"])
+        assert err.max() < 5e-14, (key, err.max())
+    assert abs(oracle.energy(pm, v) - float(GOLD[f"rnd{n}_E0"])) < 1e-13 * abs(float(GOLD[f"rnd{n}_E0"]))
+    p, w = oracle.step(pm, v, VV, PAIRWISE, 0.01, 20)
+    np.testing.assert_allclose(p, GOLD[f"rnd{n}_vv_pm"], rtol=0, atol=1e-11)
+    np.testing.assert_allclose(w, GOLD[f"rnd{n}_vv_v"], rtol=0, atol=1e-11)
+    p, w = oracle.step(pm, v, EULER, ADAPTIVE, 0.01, 20)
+    np.testing.assert_allclose(p, GOLD[f"rnd{n}_eu_pm"], rtol=0, atol=1e-11)
+    np.testing.assert_allclose(w, GOLD[f"rnd{n}_eu_v"], rtol=0, atol=1e-11)
+
+
+def test_golden_cutoff_and_duplicates(oracle):
+    pm = GOLD["cut_pm"]
+    for key, method in (("pairwise", PAIRWISE), ("adaptive", ADAPTIVE)):
+        a = oracle.forces(pm, method)
+        assert np.all(np.isfinite(a))
+        assert nbtest.rel_err(a, GOLD[f"cut_{key}"]).max() < 1e-14
+    # the 3e-6 AU pair (r^2 = 9e-12 < 1e-10) is skipped: body 0 feels only bodies 2..4
+    a = oracle.forces(pm, PAIRWISE)
+    others = pm[2:]
+    d = others[:, :3] - pm[0, :3]
+    expect = (nbtest.G * others[:, 3:4] * d / np.linalg.norm(d, axis=1, keepdims=True) ** 3).sum(0)
+    np.testing.assert_allclose(a[0], expect, rtol=1e-13)
+
+
+def test_golden_galaxy_with_planets(oracle):
+    pm = GOLD["gal_pm"]
+    assert abs(oracle.average_mass(pm) - float(GOLD["gal_avg_mass"])) < 1e-12 * float(GOLD["gal_avg_mass"])
+    for key, method in (("pairwise", PAIRWISE), ("adaptive", ADAPTIVE)):
+        assert nbtest.rel_err(oracle.forces(pm, method), GOLD[f"gal_{key}"]).max() < 1e-12
+
+
+def test_edge_cases(oracle):
+    one = np.array([[1.0, 2.0, 3.0, 5.0]])
+    assert np.all(oracle.forces(one, PAIRWISE) == 0.0)
+    assert np.all(oracle.forces(one, ADAPTIVE) == 0.0)
+    assert oracle.average_mass(np.zeros((0, 4))) == 1.0        # core/Forces.cpp:87-89
+    assert oracle.l.nbo_forces(1, one.ctypes.data_as(nbtest._dp), nbtest.BARNES_HUT,
+                               np.zeros(3).ctypes.data_as(nbtest._dp)) != 0
+    # two bodies: equal and opposite forces scaled by the masses
+    two = np.array([[0, 0, 0, 2.0], [3, 4, 0, 1.0]])
+    a = oracle.forces(two, PAIRWISE)
+    np.testing.assert_allclose(a[0] * 2.0, -a[1] * 1.0, rtol=1e-15)
+    np.testing.assert_allclose(np.linalg.norm(a[0]), nbtest.G * 1.0 / 25.0, rtol=1e-15)
+
+
+def test_thread_count_independence(oracle):
+    pm, _ = nbtest.gen_random(500, seed=1)
+    oracle.set_threads(1); a1 = oracle.forces(pm, PAIRWISE)
+    oracle.set_threads(4); a4 = oracle.forces(pm, PAIRWISE)
+    oracle.set_threads(oracle.max_threads())
+    assert np.array_equal(a1, a4)
+
+
+def test_subset_arbiter(oracle):
+    pm, _ = nbtest.gen_spiral(3000, seed=5)
+    idx = np.array([0, 17, 2999, 1500])
+    for method in (PAIRWISE, ADAPTIVE):
+        full = oracle.forces(pm, method)
+        sub = oracle.forces_subset(pm, method, idx)
+        assert nbtest.rel_err(sub, full[idx]).max() < 1e-13
+
+
+# ---- direct comparison with the compiled reference (skipped where oracle/_ref is absent) ---------------------------
+@pytest.mark.parametrize("gen,n", [("random", 700), ("spiral", 1000), ("galaxy", 100)])
+def test_oracle_vs_reference_forces(oracle, ref, gen, n):
+    pm, v = {"random": lambda: nbtest.gen_random(n, seed=11), "spiral": lambda: nbtest.gen_spiral(n, seed=11),
+             "galaxy": lambda: nbtest.gen_galaxy(n, 2, seed=11)}[gen]()
+    for method in (PAIRWISE, ADAPTIVE):
+        err = nbtest.rel_err(oracle.forces(pm, method), ref.forces(pm, method))
+        assert err.max() < 1e-12, (gen, method, err.max())
+    assert abs(oracle.energy(pm, v) - ref.energy(pm, v)) <= 1e-11 * abs(ref.energy(pm, v))   # summation order
+    assert oracle.average_mass(pm) == pytest.approx(ref.average_mass(pm), rel=1e-15)
+
+
+@pytest.mark.parametrize("integ,force", [(VV, PAIRWISE), (VV, ADAPTIVE), (EULER, PAIRWISE), (EULER, ADAPTIVE)])
+def test_oracle_vs_reference_steps(oracle, ref, integ, force):
+    pm, v = nbtest.gen_random(200, seed=3)
+    p1, v1 = oracle.step(pm, v, integ, force, 0.01, 25)
+    p2, v2 = ref.run(pm, v, integ, force, 0.01, 25)
+    np.testing.assert_allclose(p1, p2, rtol=0, atol=1e-11)
+    np.testing.assert_allclose(v1, v2, rtol=0, atol=1e-11)
+
+
+def test_reference_generators_match_seeded_distributions(ref):
+    """The seeded numpy generators used by tests/bench have the reference generators' distributions."""
+    rp, rv = ref.init_spiral(4000)
+    gp, gv = nbtest.gen_spiral(4000, seed=9)
+    assert rp[:, 3] == pytest.approx(gp[:, 3])
+    for a, b in ((rp, gp), (rv, gv)):
+        ra, rb = np.linalg.norm(a[:, :3], axis=1), np.linalg.norm(b[:, :3], axis=1)
+        assert abs(ra.mean() - rb.mean()) < 0.05 * rb.mean()
+        assert abs(ra.max() - rb.max()) < 0.05 * rb.max()
+    rp, rv = ref.init_random(500)
+    gp, gv = nbtest.gen_random(500, seed=9)
+    assert np.abs(rp[:, :3]).max() <= 50 and np.abs(gp[:, :3]).max() <= 50
+    assert abs(rp[:, 3].mean() - gp[:, 3].mean()) < 0.15 * gp[:, 3].mean()
