@@ -127,7 +127,9 @@ def test_energy_and_momentum_drift_match_reference(lib, oracle, prec):
     d_ref = float(GOLD["sis_E2500_vv_pw"]) - e0
     d_gpu = eg1 - eg0
     assert abs(d_gpu - d_ref) <= 0.01 * abs(d_ref), (d_gpu, d_ref)
-    assert np.linalg.norm(mom[:3]) < 1e-12            # COM velocity removed every step (reference: 1.4e-18)
+    # COM velocity is removed at the start of every step; what is left is one kick's worth of sum(m a) dt, which is
+    # zero only to the accuracy of the pair arithmetic (reference FP64 CPU path: 1.4e-18)
+    assert np.linalg.norm(mom[:3]) < (1e-10 if prec == FP32 else 1e-15)
     assert mom[3] == pytest.approx(pm[:, 3].sum(), rel=1e-14)
 
 
