@@ -67,17 +67,20 @@ int nb_partition_bounds(long n, int rank, int world, long* i_begin, long* i_coun
 int nb_comm_unique_id(void* id128);                               /* 128-byte ncclUniqueId, rank 0 creates it */
 int nb_comm_init(nb_ctx* ctx, const void* id128, int rank, int world);
 
-/* Host -> device of the whole system (cuda/BenchmarkKernels.cu:40-41). Buffers may be pinned or pageable. */
+/* Host -> device of the whole system (cuda/BenchmarkKernels.cu:40-41). Buffers may be pinned or pageable. On the device
+ * the particles are kept in Morton (Z-curve) order so that a tile of 256 consecutive particles is spatially compact;
+ * every entry point that returns per-particle data applies the inverse permutation, so callers only ever see their
+ * own order. Multi-GPU: every rank uploads the whole system (all ranks must pass identical arrays). */
 int nb_upload(nb_ctx* ctx, const double* posMass4, const double* vel4);
-/* Device -> host of the final state (cuda/BenchmarkKernels.cu:101-102). Multi-GPU: only this rank's slice is
- * written (rows i_begin .. i_begin+i_count of the full-size arrays). */
+/* Device -> host of the final state (cuda/BenchmarkKernels.cu:101-102), all n rows, caller order. Multi-GPU: collective
+ * (the slices are all-gathered first), every rank receives the complete state. */
 int nb_download(nb_ctx* ctx, double* posMass4, double* vel4);
 
 /* a = F(x) for the current positions: the initial launchForceKernel of cuda/BenchmarkKernels.cu:68 /
  * cuda/ForceKernels.cu:208-232. Must precede the first nb_step after an upload (nb_step does it if missing). */
 int nb_compute_accel(nb_ctx* ctx);
 /* Parity hook: copy accelerations to the host as n x double4 (ax,ay,az,0), the layout of the reference's d_accel
- * (cuda/ForceKernels.cu:94). Multi-GPU: only this rank's rows are written. */
+ * (cuda/ForceKernels.cu:94), caller order. Multi-GPU: collective, every rank receives all rows. */
 int nb_get_accel(nb_ctx* ctx, double* accel4);
 
 /* nsteps x performGPUIntegrationStep (cuda/IntegrationKernels.cu:200-266). Asynchronous: returns after enqueueing;
@@ -111,7 +114,13 @@ int nb_force_timing(nb_ctx* ctx, int reset, float* mean_ms, int* evals);
  * time in ms of everything the context enqueued in between. */
 int nb_timer_start(nb_ctx* ctx);
 int nb_timer_stop(nb_ctx* ctx, float* ms);
-/* Tuning knobs (optional): "force_variant" 0 auto | 1 plain-load tiles | 2 bulk-copy (TMA) tiles; "j_splits" 0 auto. */
+/* Tuning knobs (optional; set before nb_upload):
+ *   "force_variant"    0 auto (= 2) | 1 plain-load tiles, global hi+lo coordinates for every tile (simple, slower)
+ *                      | 2 bulk-copy (TMA) tiles re-expressed in the i-block's own frame, far tiles hi-only
+ *   "j_splits"         0 auto | 1..64 CTAs sharing one i-block's j-range
+ *   "spatial_sort"     1 (default) Morton-order the particles at upload | 0 keep the caller's order
+ *   "far_kappa_milli"  1000*kappa of the far-tile criterion box gap > kappa*(half-extent_i + half-extent_j)
+ *                      (default 1000); 0 = always use the accurate two-float path */
 int nb_set_option(nb_ctx* ctx, const char* key, long value);
 
 /* ---- whole-run entry points with HOST buffers: what the reference's host code binds ------------------------------ */

@@ -26,9 +26,12 @@ constexpr double kR2Cut    = 1e-10;   // core/Forces.cpp:144,350 — pairs with 
 //   row 3     gm         (float)(G * m)
 //   row 4..6  xl yl zl   low parts                   (float)(x - (double)xh)
 //   row 7     mq         (float)(m / (3 * mean mass))   (ADAPTIVE_MUTUAL only)
+//   row 8     meta       [0..2] bbox min, [3..5] bbox max of the tile's hi positions, [6] max |coordinate|; rest unused.
+//                        Travels with the tile (bulk copy, all-gather) so the kernel can pick the cheap path per tile.
 constexpr int kTJ = 256;                 // j-particles per tile == threads per CTA
-constexpr int kNC = 8;                   // rows per tile
-constexpr int kTileFloats = kTJ * kNC;   // 2048 floats = 8192 bytes
+constexpr int kNC = 9;                   // rows per tile
+constexpr int kMetaRow = 8;
+constexpr int kTileFloats = kTJ * kNC;   // 2304 floats = 9216 bytes
 constexpr int kTileBytes  = kTileFloats * 4;
 constexpr int kAlign = 1024;             // particle counts are padded to a multiple of this (4 tiles)
 constexpr int kThreads = 256;
@@ -39,6 +42,7 @@ struct ForceLaunch {          // one launch = i-tiles [it0, it0+nit) against the
     int ntiles;               // tiles in the whole padded system
     long npad;                // padded particle count (row stride of `part`)
     int s0, S;                // this launch writes partial slots s0 .. s0+S-1
+    float kappa;              // far-tile criterion: box gap > kappa * (|x|max_i + |x|max_j); huge = always accurate path
 };
 
 // Set thread-local error text; returns code.
@@ -73,5 +77,21 @@ int launch_accel_export(const double* acc, long npad, long first, long count, do
 int launch_accel_import_sum(const double* part, int S, long npad, long n, double4* out, cudaStream_t st);
 int launch_mass_sum(const double4* pos, long n, double* red_part, double* red, cudaStream_t st);
 int launch_momentum(const double4* pos, const double4* vel, long first, long count, double* red_part, double* red, cudaStream_t st);
+
+// nb_sort.cu
+struct SortScratch {
+    unsigned long long *keys_in = nullptr, *keys_out = nullptr;
+    unsigned int* idx_in = nullptr;
+    double *extent_part = nullptr, *box = nullptr;
+    void* cub_temp = nullptr; size_t cub_bytes = 0;
+};
+size_t sort_temp_bytes(long n);
+int build_permutation(const double4* src_pos, long n, bool spatial, SortScratch& S, unsigned int* perm, cudaStream_t st);
+int launch_gather_state(const double4* src_pos, const double4* src_vel, const unsigned int* perm, long n, long npad,
+                        double4* pos, double4* vel, cudaStream_t st);
+int launch_scatter4(const double4* src, const unsigned int* perm, long first, long count, double4* dst, cudaStream_t st);
+int launch_scatter_acc(const double* acc, long npad, const unsigned int* perm, long first, long count, double4* dst, cudaStream_t st);
+int launch_snapshot_scatter(const double4* pos, const double4* vel, const unsigned int* perm, long n,
+                            double* particleData6, double* staticData2, cudaStream_t st);
 
 } // namespace nb

@@ -70,7 +70,10 @@ struct nb_ctx {
     static constexpr int kRing = 64;
     cudaEvent_t fev0[kRing] = {}, fev1[kRing] = {};   // ring of force-evaluation event pairs
     long fev_count = 0;
-    double4 *pos = nullptr, *vel = nullptr, *tmp4 = nullptr;
+    double4 *pos = nullptr, *vel = nullptr, *tmp4 = nullptr, *stage_pos = nullptr, *stage_vel = nullptr;
+    unsigned int* perm = nullptr;          // perm[sorted slot] = caller index
+    SortScratch ss;
+    int spatial_sort = 1; float kappa = 1.0f;
     double *acc = nullptr, *part = nullptr, *red_part = nullptr, *red = nullptr, *eout = nullptr;
     float* pk = nullptr;
     size_t part_bytes = 0;
@@ -82,6 +85,53 @@ struct nb_ctx {
 };
 
 namespace {
+
+void free_arrays(nb_ctx* c) {
+    cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->tmp4); cudaFree(c->stage_pos); cudaFree(c->stage_vel);
+    cudaFree(c->acc); cudaFree(c->part); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->perm);
+    cudaFree(c->ss.keys_in); cudaFree(c->ss.keys_out); cudaFree(c->ss.idx_in); cudaFree(c->ss.extent_part);
+    cudaFree(c->ss.box); cudaFree(c->ss.cub_temp);
+    c->pos = c->vel = c->tmp4 = c->stage_pos = c->stage_vel = nullptr;
+    c->acc = c->part = c->red_part = nullptr; c->pk = nullptr; c->perm = nullptr; c->part_bytes = 0;
+    c->ss = SortScratch();
+    cudaGetLastError();
+}
+
+// Everything whose size depends on npad (the padded particle count).
+int alloc_arrays(nb_ctx* c) {
+    const size_t np = (size_t)c->npad, n = (size_t)c->n;
+    NB_CUDA(cudaMalloc(&c->pos, np * sizeof(double4)));
+    NB_CUDA(cudaMalloc(&c->vel, np * sizeof(double4)));
+    NB_CUDA(cudaMalloc(&c->tmp4, np * sizeof(double4)));
+    NB_CUDA(cudaMalloc(&c->stage_pos, n * sizeof(double4)));
+    NB_CUDA(cudaMalloc(&c->stage_vel, n * sizeof(double4)));
+    NB_CUDA(cudaMalloc(&c->acc, np * 3 * sizeof(double)));
+    NB_CUDA(cudaMalloc(&c->red_part, (np / kThreads) * 4 * sizeof(double)));
+    NB_CUDA(cudaMalloc(&c->perm, np * sizeof(unsigned int)));
+    NB_CUDA(cudaMalloc(&c->ss.keys_in, n * sizeof(unsigned long long)));
+    NB_CUDA(cudaMalloc(&c->ss.keys_out, n * sizeof(unsigned long long)));
+    NB_CUDA(cudaMalloc(&c->ss.idx_in, n * sizeof(unsigned int)));
+    NB_CUDA(cudaMalloc(&c->ss.extent_part, (np / kThreads) * 6 * sizeof(double)));
+    NB_CUDA(cudaMalloc(&c->ss.box, 8 * sizeof(double)));
+    c->ss.cub_bytes = sort_temp_bytes((long)n);
+    NB_CUDA(cudaMalloc(&c->ss.cub_temp, c->ss.cub_bytes ? c->ss.cub_bytes : 16));
+    if (c->precision == NB_PREC_FP32) {
+        NB_CUDA(cudaMalloc(&c->pk, np * kNC * sizeof(float)));
+        NB_CUDA(cudaMemsetAsync(c->pk, 0, np * kNC * sizeof(float), c->stream));
+    }
+    NB_CUDA(cudaMemsetAsync(c->pos, 0, np * sizeof(double4), c->stream));
+    NB_CUDA(cudaMemsetAsync(c->vel, 0, np * sizeof(double4), c->stream));
+    NB_CUDA(cudaMemsetAsync(c->acc, 0, np * 3 * sizeof(double), c->stream));
+    return NB_OK;
+}
+
+// Caller-order device arrays (n rows) -> Morton-ordered, padded master state + packed tiles.
+int ingest(nb_ctx* c, const double4* src_pos, const double4* src_vel) {
+    int rc = build_permutation(src_pos, c->n, c->spatial_sort != 0, c->ss, c->perm, c->stream); if (rc) return rc;
+    rc = launch_gather_state(src_pos, src_vel, c->perm, c->n, c->npad, c->pos, c->vel, c->stream); if (rc) return rc;
+    c->launches += 5;
+    return NB_OK;
+}
 
 StepArrays arrays(nb_ctx* c) {
     StepArrays A;
@@ -123,7 +173,7 @@ int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const 
     const bool adaptive = (c->force == NB_FORCE_ADAPTIVE_MUTUAL);
     int rc;
     if (c->precision == NB_PREC_FP32) {
-        const int variant = c->force_variant == 0 ? 1 : c->force_variant;
+        const int variant = c->force_variant == 0 ? 2 : c->force_variant;
         rc = launch_force_fp32(pk, part, L, adaptive, variant, c->stream);
     } else {
         rc = launch_force_fp64(pos, part, L, adaptive, c->avg_mass, c->stream);
@@ -139,6 +189,7 @@ int eval_force(nb_ctx* c, int* S_out) {
     const int nit = (int)(c->ni / kTJ), it0 = (int)(c->i0 / kTJ);
     const int iblocks = nit / R;
     ForceLaunch L; L.it0 = it0; L.nit = nit; L.ntiles = c->ntiles; L.npad = c->npad;
+    L.kappa = c->kappa > 0.f ? c->kappa : 3.0e38f;
     const int slot = (int)(c->fev_count % nb_ctx::kRing);
     NB_CUDA(cudaEventRecord(c->fev0[slot], c->stream));
     if (c->world == 1) {
@@ -248,17 +299,10 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
     NB_TRY(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
     NB_TRY(cudaEventCreate(&c->tev0)); NB_TRY(cudaEventCreate(&c->tev1));
     for (int k = 0; k < nb_ctx::kRing; ++k) { NB_TRY(cudaEventCreate(&c->fev0[k])); NB_TRY(cudaEventCreate(&c->fev1[k])); }
-    NB_TRY(cudaMalloc(&c->pos, (size_t)c->npad * sizeof(double4)));
-    NB_TRY(cudaMalloc(&c->vel, (size_t)c->npad * sizeof(double4)));
-    NB_TRY(cudaMalloc(&c->acc, (size_t)c->npad * 3 * sizeof(double)));
-    NB_TRY(cudaMalloc(&c->red_part, (size_t)(c->npad / kThreads) * 4 * sizeof(double)));
     NB_TRY(cudaMalloc(&c->red, 16 * sizeof(double)));
     NB_TRY(cudaMalloc(&c->eout, 16 * sizeof(double)));
-    if (precision == NB_PREC_FP32) NB_TRY(cudaMalloc(&c->pk, (size_t)c->npad * kNC * sizeof(float)));
-    NB_TRY(cudaMemsetAsync(c->pos, 0, (size_t)c->npad * sizeof(double4), c->stream));
-    NB_TRY(cudaMemsetAsync(c->vel, 0, (size_t)c->npad * sizeof(double4), c->stream));
-    NB_TRY(cudaMemsetAsync(c->acc, 0, (size_t)c->npad * 3 * sizeof(double), c->stream));
     NB_TRY(cudaMemsetAsync(c->red, 0, 16 * sizeof(double), c->stream));
+    { int rc = alloc_arrays(c); if (rc) return bail(rc); }
 #undef NB_TRY
     *out = c;
     return NB_OK;
@@ -270,8 +314,8 @@ int nb_destroy(nb_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     if (c->comm && nccl::CommDestroy) nccl::CommDestroy(c->comm);
-    cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->tmp4); cudaFree(c->acc); cudaFree(c->part);
-    cudaFree(c->red_part); cudaFree(c->red); cudaFree(c->eout); cudaFree(c->pk);
+    free_arrays(c);
+    cudaFree(c->red); cudaFree(c->eout);
     if (c->ev_packed) cudaEventDestroy(c->ev_packed);
     if (c->ev_gathered) cudaEventDestroy(c->ev_gathered);
     if (c->tev0) cudaEventDestroy(c->tev0);
@@ -297,6 +341,8 @@ int nb_set_option(nb_ctx* c, const char* key, long value) {
     if (!c || !key) return fail(NB_ERR_INVALID, "nb_set_option: NULL argument");
     if (!strcmp(key, "force_variant")) { if (value < 0 || value > 2) return fail(NB_ERR_INVALID, "force_variant must be 0..2"); c->force_variant = (int)value; return NB_OK; }
     if (!strcmp(key, "j_splits")) { if (value < 0 || value > 64) return fail(NB_ERR_INVALID, "j_splits must be 0..64"); c->j_splits = (int)value; return NB_OK; }
+    if (!strcmp(key, "spatial_sort")) { c->spatial_sort = value ? 1 : 0; return NB_OK; }
+    if (!strcmp(key, "far_kappa_milli")) { if (value < 0) return fail(NB_ERR_INVALID, "far_kappa_milli must be >= 0"); c->kappa = (float)value * 1e-3f; return NB_OK; }
     return fail(NB_ERR_INVALID, "nb_set_option: unknown key '%s'", key);
 }
 
@@ -319,23 +365,11 @@ int nb_comm_init(nb_ctx* c, const void* id128, int rank, int world) {
     // equal, tile-aligned slices; the padded system grows to world * per
     const long per = round_up(round_up(c->n, world) / world, kAlign);
     const long npad = per * world;
-    if (npad != c->npad) {
-        // re-allocate for the larger padding
-        const long n = c->n; const int dev = c->device, prec = c->precision;
-        const int integ = c->integ, force = c->force, sub = c->subtract_com, fv = c->force_variant, js = c->j_splits;
+    if (npad != c->npad) {             // equal slices need a larger padding: re-allocate everything sized by npad
         NB_CUDA(cudaStreamSynchronize(c->stream));
-        cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->acc); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->part); cudaFree(c->tmp4);
-        c->pos = c->vel = c->tmp4 = nullptr; c->acc = c->red_part = c->part = nullptr; c->pk = nullptr; c->part_bytes = 0;
+        free_arrays(c);
         c->npad = npad; c->ntiles = (int)(npad / kTJ);
-        NB_CUDA(cudaMalloc(&c->pos, (size_t)npad * sizeof(double4)));
-        NB_CUDA(cudaMalloc(&c->vel, (size_t)npad * sizeof(double4)));
-        NB_CUDA(cudaMalloc(&c->acc, (size_t)npad * 3 * sizeof(double)));
-        NB_CUDA(cudaMalloc(&c->red_part, (size_t)(npad / kThreads) * 4 * sizeof(double)));
-        if (prec == NB_PREC_FP32) NB_CUDA(cudaMalloc(&c->pk, (size_t)npad * kNC * sizeof(float)));
-        NB_CUDA(cudaMemsetAsync(c->pos, 0, (size_t)npad * sizeof(double4), c->stream));
-        NB_CUDA(cudaMemsetAsync(c->vel, 0, (size_t)npad * sizeof(double4), c->stream));
-        NB_CUDA(cudaMemsetAsync(c->acc, 0, (size_t)npad * 3 * sizeof(double), c->stream));
-        (void)n; (void)dev; (void)integ; (void)force; (void)sub; (void)fv; (void)js;
+        rc = alloc_arrays(c); if (rc) return rc;
     }
     c->i0 = per * rank; c->ni = per;
     rc = nccl::load(); if (rc) return rc;
@@ -347,12 +381,13 @@ int nb_comm_init(nb_ctx* c, const void* id128, int rank, int world) {
 int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
     if (!c || !posMass4 || !vel4) return fail(NB_ERR_INVALID, "nb_upload: NULL argument");
     int rc = use_device(c); if (rc) return rc;
-    NB_CUDA(cudaMemcpyAsync(c->pos, posMass4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
-    NB_CUDA(cudaMemcpyAsync(c->vel, vel4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(c->stage_pos, posMass4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(c->stage_vel, vel4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
     // computeAverageMass (core/Forces.cpp:85-95): serial sum in index order on the host, exactly as the reference.
     double total = 0.0;
     for (long i = 0; i < c->n; ++i) total += posMass4[4 * i + 3];
     c->avg_mass = total / (double)c->n;
+    rc = ingest(c, c->stage_pos, c->stage_vel); if (rc) return rc;
     StepArrays A = arrays(c);
     rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream); if (rc) return rc;
     c->launches++;
@@ -361,15 +396,28 @@ int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
     return NB_OK;
 }
 
+namespace {
+// Multi-GPU: make every rank's copy of the (Morton-ordered) master state complete before it leaves the device.
+int gather_state_all(nb_ctx* c) {
+    if (c->world == 1) return NB_OK;
+    const size_t count = (size_t)c->ni * 4;
+    NB_NCCL(nccl::AllGather((const double*)(c->pos + c->i0), (double*)c->pos, count, nccl::kFloat64, c->comm, c->stream));
+    NB_NCCL(nccl::AllGather((const double*)(c->vel + c->i0), (double*)c->vel, count, nccl::kFloat64, c->comm, c->stream));
+    return NB_OK;
+}
+}
+
 int nb_download(nb_ctx* c, double* posMass4, double* vel4) {
     if (!c || !posMass4 || !vel4) return fail(NB_ERR_INVALID, "nb_download: NULL argument");
     if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_download before nb_upload");
     int rc = use_device(c); if (rc) return rc;
-    long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;
-    if (e > b) {
-        NB_CUDA(cudaMemcpyAsync(posMass4 + 4 * b, c->pos + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
-        NB_CUDA(cudaMemcpyAsync(vel4 + 4 * b, c->vel + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
-    }
+    if (c->world > 1) NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+    rc = gather_state_all(c); if (rc) return rc;
+    rc = launch_scatter4(c->pos, c->perm, 0, c->n, c->stage_pos, c->stream); if (rc) return rc;
+    rc = launch_scatter4(c->vel, c->perm, 0, c->n, c->stage_vel, c->stream); if (rc) return rc;
+    c->launches += 2;
+    NB_CUDA(cudaMemcpyAsync(posMass4, c->stage_pos, (size_t)c->n * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaMemcpyAsync(vel4, c->stage_vel, (size_t)c->n * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
@@ -389,11 +437,14 @@ int nb_get_accel(nb_ctx* c, double* accel4) {
     if (!c || !accel4) return fail(NB_ERR_INVALID, "nb_get_accel: NULL argument");
     if (!c->have_accel) return fail(NB_ERR_INVALID, "nb_get_accel before nb_compute_accel / nb_step");
     int rc = use_device(c); if (rc) return rc;
-    if (!c->tmp4) NB_CUDA(cudaMalloc(&c->tmp4, (size_t)c->npad * sizeof(double4)));
-    long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;
-    rc = launch_accel_export(c->acc, c->npad, b, e - b, c->tmp4, c->stream); if (rc) return rc;
+    if (c->world > 1) {
+        for (int k = 0; k < 3; ++k)
+            NB_NCCL(nccl::AllGather(c->acc + (size_t)k * c->npad + c->i0, c->acc + (size_t)k * c->npad, (size_t)c->ni,
+                                    nccl::kFloat64, c->comm, c->stream));
+    }
+    rc = launch_scatter_acc(c->acc, c->npad, c->perm, 0, c->n, c->tmp4, c->stream); if (rc) return rc;
     c->launches++;
-    if (e > b) NB_CUDA(cudaMemcpyAsync(accel4 + 4 * b, c->tmp4 + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaMemcpyAsync(accel4, c->tmp4, (size_t)c->n * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
@@ -428,7 +479,6 @@ int nb_energy(nb_ctx* c, double out[3]) {
     if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_energy before nb_upload");
     if (c->world > 1) return fail(NB_ERR_UNSUPPORTED, "nb_energy needs the whole system on one device (world=%d)", c->world);
     int rc = use_device(c); if (rc) return rc;
-    if (!c->tmp4) NB_CUDA(cudaMalloc(&c->tmp4, (size_t)c->npad * sizeof(double4)));
     double* pot = reinterpret_cast<double*>(c->tmp4);
     rc = launch_potential_fp64(c->pos, pot, c->npad, c->ntiles, c->stream); if (rc) return rc;
     StepArrays A = arrays(c);
@@ -470,7 +520,7 @@ int nb_snapshot(nb_ctx* c, double time, double* particleData6, double* systemDat
     double* d6 = nullptr; double* d2 = nullptr;
     NB_CUDA(cudaMalloc(&d6, (size_t)c->n * 8 * sizeof(double)));
     d2 = d6 + (size_t)c->n * 6;
-    rc = launch_snapshot(c->pos, c->vel, c->n, d6, staticData2 ? d2 : nullptr, c->stream);
+    rc = launch_snapshot_scatter(c->pos, c->vel, c->perm, c->n, d6, staticData2 ? d2 : nullptr, c->stream);
     if (rc) { cudaFree(d6); return rc; }
     c->launches++;
     cudaError_t e1 = cudaMemcpyAsync(particleData6, d6, (size_t)c->n * 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
@@ -578,22 +628,24 @@ int nb_launch_force(nb_ctx* c, int force_method, const double* d_posMass4, doubl
     // Order the context stream after the caller's stream and vice versa with events.
     cudaEvent_t ev; NB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     if (user) { NB_CUDA(cudaEventRecord(ev, user)); NB_CUDA(cudaStreamWaitEvent(c->stream, ev, 0)); }
-    NB_CUDA(cudaMemcpyAsync(c->pos, d_posMass4, (size_t)n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+    NB_CUDA(cudaMemcpyAsync(c->stage_pos, d_posMass4, (size_t)n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
     const int saved_force = c->force;
     c->force = force_method;
     if (avg_mass > 0.0) c->avg_mass = avg_mass;
     else {
-        rc = launch_mass_sum(c->pos, n, c->red_part, c->eout + 12, c->stream); if (rc) return rc;
+        rc = launch_mass_sum(c->stage_pos, n, c->red_part, c->eout + 12, c->stream); if (rc) return rc;
         double r4[4];
         NB_CUDA(cudaMemcpyAsync(r4, c->eout + 12, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
         NB_CUDA(cudaStreamSynchronize(c->stream));
         c->avg_mass = r4[3] / (double)n;
     }
+    rc = ingest(c, c->stage_pos, nullptr);
     StepArrays A = arrays(c);
-    rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream);
+    if (!rc) rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream);
     int S = 0;
     if (!rc) rc = eval_force(c, &S);
-    if (!rc) rc = launch_accel_import_sum(c->part, S, c->npad, n, reinterpret_cast<double4*>(d_accel4), c->stream);
+    if (!rc) rc = launch_accel_import_sum(c->part, S, c->npad, n, c->tmp4, c->stream);
+    if (!rc) rc = launch_scatter4(c->tmp4, c->perm, 0, n, reinterpret_cast<double4*>(d_accel4), c->stream);
     c->force = saved_force; c->have_accel = false; c->uploaded = true;
     if (rc) { cudaEventDestroy(ev); return rc; }
     c->launches += 2;

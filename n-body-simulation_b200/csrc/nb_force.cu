@@ -51,27 +51,37 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// One j4 group (four consecutive j-particles = two packed pairs) against the R register-resident i-particles.
+// Register-resident i-particles: R per thread, every value duplicated into both halves of a register pair so that one
+// packed instruction handles two j-particles.
 template <int R, bool ADAPTIVE>
 struct IState {
-    float2 nxh[R], nyh[R], nzh[R];     // -(hi position), duplicated in both halves
+    float2 nxh[R], nyh[R], nzh[R];     // -(hi position)
     float2 nxl[R], nyl[R], nzl[R];     // -(lo position)
     float2 mq[R];                      // m_i / (3 mean mass) (ADAPTIVE)
     float2 ax[R], ay[R], az[R];        // FP32 partial sums (.x: even j, .y: odd j)
     double dax[R], day[R], daz[R];     // FP64 running sums
 };
 
-template <int R, bool ADAPTIVE>
-__device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* __restrict__ tile, int j4) {
-    const float4 XH = reinterpret_cast<const float4*>(tile + 0 * kTJ)[j4];
-    const float4 YH = reinterpret_cast<const float4*>(tile + 1 * kTJ)[j4];
-    const float4 ZH = reinterpret_cast<const float4*>(tile + 2 * kTJ)[j4];
-    const float4 GM = reinterpret_cast<const float4*>(tile + 3 * kTJ)[j4];
-    const float4 XL = reinterpret_cast<const float4*>(tile + 4 * kTJ)[j4];
-    const float4 YL = reinterpret_cast<const float4*>(tile + 5 * kTJ)[j4];
-    const float4 ZL = reinterpret_cast<const float4*>(tile + 6 * kTJ)[j4];
+// One j4 group (four consecutive j-particles = two packed pairs) against the R i-particles.
+//   hi, lo : 3 rows (x,y,z) of kTJ floats each;  gm, mq : one row each.
+// FAR (only used in the i-block-relative frame of variant 2): the hi parts alone carry d to ~3e-7 and no pair of the
+// tile can be a self pair or inside the cut-off, so the lo adds and the compare/select are dropped:
+// 12 instead of 18 FP32-pipe operations per interaction.
+template <int R, bool ADAPTIVE, bool FAR>
+__device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* __restrict__ hi, const float* __restrict__ lo,
+                                          const float* __restrict__ gmrow, const float* __restrict__ mqrow, int j4) {
+    const float4 XH = reinterpret_cast<const float4*>(hi + 0 * kTJ)[j4];
+    const float4 YH = reinterpret_cast<const float4*>(hi + 1 * kTJ)[j4];
+    const float4 ZH = reinterpret_cast<const float4*>(hi + 2 * kTJ)[j4];
+    const float4 GM = reinterpret_cast<const float4*>(gmrow)[j4];
+    float4 XL = make_float4(0.f, 0.f, 0.f, 0.f), YL = XL, ZL = XL;
+    if (!FAR) {
+        XL = reinterpret_cast<const float4*>(lo + 0 * kTJ)[j4];
+        YL = reinterpret_cast<const float4*>(lo + 1 * kTJ)[j4];
+        ZL = reinterpret_cast<const float4*>(lo + 2 * kTJ)[j4];
+    }
     float4 MQ = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (ADAPTIVE) MQ = reinterpret_cast<const float4*>(tile + 7 * kTJ)[j4];
+    if (ADAPTIVE) MQ = reinterpret_cast<const float4*>(mqrow)[j4];
 #pragma unroll
     for (int p = 0; p < 2; ++p) {
         const float2 xjh = p ? make_float2(XH.z, XH.w) : make_float2(XH.x, XH.y);
@@ -86,9 +96,14 @@ __device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* _
         for (int r = 0; r < R; ++r) {
             // d = (xjh - xih) + (xjl - xil): the hi difference is exact for close pairs (Sterbenz), the lo difference
             // restores the bits the FP32 rounding of the coordinates dropped.
-            const float2 dx = __fadd2_rn(__fadd2_rn(xjh, S.nxh[r]), __fadd2_rn(xjl, S.nxl[r]));
-            const float2 dy = __fadd2_rn(__fadd2_rn(yjh, S.nyh[r]), __fadd2_rn(yjl, S.nyl[r]));
-            const float2 dz = __fadd2_rn(__fadd2_rn(zjh, S.nzh[r]), __fadd2_rn(zjl, S.nzl[r]));
+            float2 dx = __fadd2_rn(xjh, S.nxh[r]);
+            float2 dy = __fadd2_rn(yjh, S.nyh[r]);
+            float2 dz = __fadd2_rn(zjh, S.nzh[r]);
+            if (!FAR) {
+                dx = __fadd2_rn(dx, __fadd2_rn(xjl, S.nxl[r]));
+                dy = __fadd2_rn(dy, __fadd2_rn(yjl, S.nyl[r]));
+                dz = __fadd2_rn(dz, __fadd2_rn(zjl, S.nzl[r]));
+            }
             float2 r2 = __fmul2_rn(dz, dz);
             r2 = __ffma2_rn(dy, dy, r2);
             r2 = __ffma2_rn(dx, dx, r2);
@@ -108,8 +123,10 @@ __device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* _
             }
             float2 ri; ri.x = rsq_approx(s2.x); ri.y = rsq_approx(s2.y);
             // cut-off (also removes the self term, for which r2 == 0 exactly): core/Forces.cpp:135,144
-            ri.x = r2.x < 1e-10f ? 0.f : ri.x;
-            ri.y = r2.y < 1e-10f ? 0.f : ri.y;
+            if (!FAR) {
+                ri.x = r2.x < 1e-10f ? 0.f : ri.x;
+                ri.y = r2.y < 1e-10f ? 0.f : ri.y;
+            }
             const float2 ri2 = __fmul2_rn(ri, ri);
             float2 sc = __fmul2_rn(gm, ri);
             sc = __fmul2_rn(sc, ri2);
@@ -120,12 +137,14 @@ __device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* _
     }
 }
 
-template <int R, bool ADAPTIVE>
-__device__ __forceinline__ void tile_pass(IState<R, ADAPTIVE>& S, const float* __restrict__ tile) {
+template <int R, bool ADAPTIVE, bool FAR>
+__device__ __forceinline__ void tile_pass(IState<R, ADAPTIVE>& S, const float* __restrict__ hi, const float* __restrict__ lo,
+                                          const float* __restrict__ gmrow, const float* __restrict__ mqrow) {
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
 #pragma unroll 2
-        for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4) interact4<R, ADAPTIVE>(S, tile, j4);
+        for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4)
+            interact4<R, ADAPTIVE, FAR>(S, hi, lo, gmrow, mqrow, j4);
 #pragma unroll
         for (int r = 0; r < R; ++r) {      // flush 128 j's of FP32 partial sums into the FP64 accumulators
             S.dax[r] += (double)(S.ax[r].x + S.ax[r].y); S.ax[r] = make_float2(0.f, 0.f);
@@ -136,18 +155,9 @@ __device__ __forceinline__ void tile_pass(IState<R, ADAPTIVE>& S, const float* _
 }
 
 template <int R, bool ADAPTIVE>
-__device__ __forceinline__ void load_i(IState<R, ADAPTIVE>& S, const float* __restrict__ pk, int itile_first, int t) {
+__device__ __forceinline__ void init_acc(IState<R, ADAPTIVE>& S) {
 #pragma unroll
     for (int r = 0; r < R; ++r) {
-        const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
-        float v;
-        v = -p[0 * kTJ]; S.nxh[r] = make_float2(v, v);
-        v = -p[1 * kTJ]; S.nyh[r] = make_float2(v, v);
-        v = -p[2 * kTJ]; S.nzh[r] = make_float2(v, v);
-        v = -p[4 * kTJ]; S.nxl[r] = make_float2(v, v);
-        v = -p[5 * kTJ]; S.nyl[r] = make_float2(v, v);
-        v = -p[6 * kTJ]; S.nzl[r] = make_float2(v, v);
-        v = ADAPTIVE ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
         S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
         S.dax[r] = S.day[r] = S.daz[r] = 0.0;
     }
@@ -166,7 +176,9 @@ __device__ __forceinline__ void store_part(const IState<R, ADAPTIVE>& S, double*
 
 __device__ __forceinline__ int wrap_tile(int jt, int ntiles) { return jt >= ntiles ? jt - ntiles : jt; }
 
-// Variant 1: j-tiles staged with plain vector loads through registers, double-buffered, one barrier per tile.
+// ------------------------------------------------------------------------------------------------------------------
+// Variant 1 (simple, always accurate): global hi+lo coordinates for every tile, strict cut-off; j-tiles staged with
+// plain vector loads through registers, double-buffered, one barrier per tile. 18 FP32-pipe operations/interaction.
 template <int R, bool ADAPTIVE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp32_ld_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
@@ -175,14 +187,28 @@ force_fp32_ld_kernel(const float* __restrict__ pk, double* __restrict__ part, co
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
     const int itile_first = L.it0 + blockIdx.x * R;
     IState<R, ADAPTIVE> S;
-    load_i<R, ADAPTIVE>(S, pk, itile_first, t);
+    init_acc<R, ADAPTIVE>(S);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
+        float v;
+        v = -p[0 * kTJ]; S.nxh[r] = make_float2(v, v);
+        v = -p[1 * kTJ]; S.nyh[r] = make_float2(v, v);
+        v = -p[2 * kTJ]; S.nzh[r] = make_float2(v, v);
+        v = -p[4 * kTJ]; S.nxl[r] = make_float2(v, v);
+        v = -p[5 * kTJ]; S.nyl[r] = make_float2(v, v);
+        v = -p[6 * kTJ]; S.nzl[r] = make_float2(v, v);
+        v = ADAPTIVE ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
+    }
     const float4* gsrc = reinterpret_cast<const float4*>(pk);
+    constexpr int kV = 8 * kTJ / 4;                // rows 0..7 of the tile (the meta row is not needed here)
     float4 g0 = make_float4(0, 0, 0, 0), g1 = g0;
     if (k0 < k1) {
         const float4* src = gsrc + (size_t)wrap_tile(L.jt0 + k0, L.ntiles) * (kTileFloats / 4);
         reinterpret_cast<float4*>(sm[0])[t] = src[t];
         reinterpret_cast<float4*>(sm[0])[t + kThreads] = src[t + kThreads];
     }
+    static_assert(kV == 2 * kThreads, "two float4 per thread");
     __syncthreads();
     for (int k = k0; k < k1; ++k) {
         const int b = (k - k0) & 1;
@@ -191,7 +217,7 @@ force_fp32_ld_kernel(const float* __restrict__ pk, double* __restrict__ part, co
             const float4* src = gsrc + (size_t)wrap_tile(L.jt0 + k + 1, L.ntiles) * (kTileFloats / 4);
             g0 = src[t]; g1 = src[t + kThreads];
         }
-        tile_pass<R, ADAPTIVE>(S, sm[b]);
+        tile_pass<R, ADAPTIVE, false>(S, sm[b], sm[b] + 4 * kTJ, sm[b] + 3 * kTJ, sm[b] + 7 * kTJ);
         if (more) {
             reinterpret_cast<float4*>(sm[b ^ 1])[t] = g0;
             reinterpret_cast<float4*>(sm[b ^ 1])[t + kThreads] = g1;
@@ -201,13 +227,76 @@ force_fp32_ld_kernel(const float* __restrict__ pk, double* __restrict__ part, co
     store_part<R, ADAPTIVE>(S, part, L, itile_first, t, s);
 }
 
-// Variant 2: j-tiles staged by the bulk-copy engine (cp.async.bulk -> UBLKCP) into a kStages-deep ring; each
-// stage has an mbarrier that the copy completes with its byte count. One thread produces, all threads consume.
-constexpr int kStages = 4;
+// ------------------------------------------------------------------------------------------------------------------
+// Variant 2 (production):
+//   * j-tiles arrive through the bulk-copy engine (cp.async.bulk -> UBLKCP) in a kStages-deep ring, each stage with an
+//     mbarrier completed by the copy's byte count; one thread produces, all threads consume;
+//   * every tile is re-expressed relative to the CTA's own origin O (centre of the bounding box of its i-particles):
+//     thread t turns particle t of the raw tile into x' = (xh - O) + xl while the previous tile is being computed.
+//     In that frame |x'| is the distance from the i-block, so for every tile whose box is further from the i-block than
+//     kappa * (half-extent_i + half-extent_j) a single float per coordinate already carries d to ~3e-7 (FAR path);
+//     only the few adjacent tiles need the two-float path (x', l') produced by an error-free TwoSum, and only they
+//     can contain self pairs or pairs inside the 1e-5 AU cut-off.
+constexpr int kStages = 3;
+constexpr int kXfRows = 6;                         // x' y' z' and l'x l'y l'z
+
+struct CtaFrame { float O[3]; float lo[3], hi[3]; float half; };
+
+template <int R>
+__device__ __forceinline__ void load_frame(CtaFrame& F, const float* __restrict__ pk, int itile_first) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { F.lo[c] = 3.0e38f; F.hi[c] = -3.0e38f; }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const float* m = pk + (size_t)(itile_first + r) * kTileFloats + kMetaRow * kTJ;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { F.lo[c] = fminf(F.lo[c], __ldg(m + c)); F.hi[c] = fmaxf(F.hi[c], __ldg(m + 3 + c)); }
+    }
+    F.half = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { F.O[c] = 0.5f * F.lo[c] + 0.5f * F.hi[c]; F.half = fmaxf(F.half, 0.5f * (F.hi[c] - F.lo[c])); }
+}
+// meta: the j-tile's meta row (shared memory). CTA-uniform.
+__device__ __forceinline__ bool tile_is_far(const CtaFrame& F, const float* __restrict__ meta, float kappa) {
+    float g2 = 0.f, hj = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float g = fmaxf(0.f, fmaxf(meta[c] - F.hi[c], F.lo[c] - meta[3 + c]));
+        g2 = fmaf(g, g, g2);
+        hj = fmaxf(hj, 0.5f * (meta[3 + c] - meta[c]));
+    }
+    const float thr = kappa * (F.half + hj);
+    return (g2 > thr * thr) && (g2 > 1e-8f);
+}
+// (h, l) = two-float value of (xh + xl) - O: TwoSum(xh, -O) is error free, the low words are then folded in.
+__device__ __forceinline__ void rel_two(float xh, float xl, float O, float& h, float& l) {
+    const float b = -O;
+    const float s = xh + b;
+    const float bb = s - xh;
+    const float e = (xh - (s - bb)) + (b - bb);
+    const float u = e + xl;
+    h = s + u;
+    l = u - (h - s);
+}
+template <bool FAR>
+__device__ __forceinline__ void transform_tile(const float* __restrict__ raw, float* __restrict__ T, const CtaFrame& F, int t) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float xh = raw[c * kTJ + t], xl = raw[(4 + c) * kTJ + t];
+        if (FAR) {
+            T[c * kTJ + t] = (xh - F.O[c]) + xl;
+        } else {
+            float h, l; rel_two(xh, xl, F.O[c], h, l);
+            T[c * kTJ + t] = h; T[(3 + c) * kTJ + t] = l;
+        }
+    }
+}
+
 template <int R, bool ADAPTIVE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
-    __shared__ __align__(128) float sm[kStages][kTileFloats];
+    __shared__ __align__(128) float raw[kStages][kTileFloats];
+    __shared__ __align__(16) float T[2][kXfRows * kTJ];
     __shared__ __align__(8) uint64_t full[kStages];
     const int t = threadIdx.x, s = blockIdx.y;
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
@@ -223,21 +312,49 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
         const int pre = cnt < kStages ? cnt : kStages;
         for (int q = 0; q < pre; ++q) {
             mbar_expect_tx(&full[q], kTileBytes);
-            bulk_g2s(sm[q], pk + (size_t)wrap_tile(L.jt0 + k0 + q, L.ntiles) * kTileFloats, kTileBytes, &full[q]);
+            bulk_g2s(raw[q], pk + (size_t)wrap_tile(L.jt0 + k0 + q, L.ntiles) * kTileFloats, kTileBytes, &full[q]);
         }
     }
+    CtaFrame F;
+    load_frame<R>(F, pk, itile_first);
     IState<R, ADAPTIVE> S;
-    load_i<R, ADAPTIVE>(S, pk, itile_first, t);
+    init_acc<R, ADAPTIVE>(S);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {      // own i-particles in the CTA frame, as two-float values
+        const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
+        float h, l;
+        rel_two(p[0 * kTJ], p[4 * kTJ], F.O[0], h, l); S.nxh[r] = make_float2(-h, -h); S.nxl[r] = make_float2(-l, -l);
+        rel_two(p[1 * kTJ], p[5 * kTJ], F.O[1], h, l); S.nyh[r] = make_float2(-h, -h); S.nyl[r] = make_float2(-l, -l);
+        rel_two(p[2 * kTJ], p[6 * kTJ], F.O[2], h, l); S.nzh[r] = make_float2(-h, -h); S.nzl[r] = make_float2(-l, -l);
+        const float v = ADAPTIVE ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
+    }
+    bool far_cur = false;
+    if (cnt > 0) {
+        mbar_wait(&full[0], 0u);
+        far_cur = tile_is_far(F, raw[0] + kMetaRow * kTJ, L.kappa);
+        if (far_cur) transform_tile<true>(raw[0], T[0], F, t); else transform_tile<false>(raw[0], T[0], F, t);
+    }
+    __syncthreads();
     for (int q = 0; q < cnt; ++q) {
         const int b = q % kStages;
-        mbar_wait(&full[b], (uint32_t)((q / kStages) & 1));
-        tile_pass<R, ADAPTIVE>(S, sm[b]);
-        __syncthreads();                       // every warp is done reading stage b
+        bool far_next = false;
+        if (q + 1 < cnt) {                 // re-express the next tile while this one is being computed
+            const int bn = (q + 1) % kStages;
+            mbar_wait(&full[bn], (uint32_t)(((q + 1) / kStages) & 1));
+            far_next = tile_is_far(F, raw[bn] + kMetaRow * kTJ, L.kappa);
+            float* Tn = T[(q + 1) & 1];
+            if (far_next) transform_tile<true>(raw[bn], Tn, F, t); else transform_tile<false>(raw[bn], Tn, F, t);
+        }
+        const float* Tc = T[q & 1];
+        if (far_cur) tile_pass<R, ADAPTIVE, true>(S, Tc, Tc + 3 * kTJ, raw[b] + 3 * kTJ, raw[b] + 7 * kTJ);
+        else         tile_pass<R, ADAPTIVE, false>(S, Tc, Tc + 3 * kTJ, raw[b] + 3 * kTJ, raw[b] + 7 * kTJ);
+        __syncthreads();                   // every warp is done with raw[b] and T[q&1]; T[(q+1)&1] is complete
         if (t == 0 && q + kStages < cnt) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_expect_tx(&full[b], kTileBytes);
-            bulk_g2s(sm[b], pk + (size_t)wrap_tile(L.jt0 + k0 + q + kStages, L.ntiles) * kTileFloats, kTileBytes, &full[b]);
+            bulk_g2s(raw[b], pk + (size_t)wrap_tile(L.jt0 + k0 + q + kStages, L.ntiles) * kTileFloats, kTileBytes, &full[b]);
         }
+        far_cur = far_next;
     }
     store_part<R, ADAPTIVE>(S, part, L, itile_first, t, s);
 }

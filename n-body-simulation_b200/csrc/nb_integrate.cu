@@ -45,41 +45,68 @@ __device__ __forceinline__ void pack_one(float* __restrict__ pk, long i, const d
     o[7 * kTJ] = (float)(p.w * inv3mbar);
 }
 
-__global__ void __launch_bounds__(kThreads)
-pack_kernel(const double4* __restrict__ pos, float* __restrict__ pk, long first, long count, double inv3mbar) {
-    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
-    if (k < count) pack_one(pk, first + k, pos[first + k], inv3mbar);
+// Bounding box of the tile this CTA just packed (one CTA == one tile of kTJ particles) -> meta row of the tile.
+__device__ __forceinline__ void tile_meta(float* __restrict__ pk, long tile, float x, float y, float z) {
+    __shared__ float shm[7][kThreads / 32];
+    float v[7] = {x, y, z, x, y, z, fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)))};
+#pragma unroll
+    for (int c = 0; c < 7; ++c) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const float w = __shfl_xor_sync(0xffffffffu, v[c], o);
+            v[c] = c < 3 ? fminf(v[c], w) : fmaxf(v[c], w);
+        }
+        if ((threadIdx.x & 31) == 0) shm[c][threadIdx.x >> 5] = v[c];
+    }
+    __syncthreads();
+    if (threadIdx.x < 7) {
+        const int c = threadIdx.x;
+        float r = shm[c][0];
+        for (int k = 1; k < kThreads / 32; ++k) r = c < 3 ? fminf(r, shm[c][k]) : fmaxf(r, shm[c][k]);
+        pk[(size_t)tile * kTileFloats + kMetaRow * kTJ + c] = r;
+    }
 }
 
-// drift: one thread per owned particle.
+// `first` and `count` are multiples of kTJ: CTA b packs tile first/kTJ + b.
+__global__ void __launch_bounds__(kThreads)
+pack_kernel(const double4* __restrict__ pos, float* __restrict__ pk, long first, long count, double inv3mbar) {
+    const long i = first + (long)blockIdx.x * kThreads + threadIdx.x;
+    const double4 p = pos[i];
+    pack_one(pk, i, p, inv3mbar);
+    tile_meta(pk, i / kTJ, (float)p.x, (float)p.y, (float)p.z);
+}
+
+// drift: one thread per owned particle; one CTA == one tile (A.i0 and A.ni are multiples of kTJ).
 template <int INTEG>
 __global__ void __launch_bounds__(kThreads)
 drift_kernel(StepArrays A, double dt, int subtract_com, double inv3mbar) {
-    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
-    if (k >= A.ni) return;
-    const long i = A.i0 + k;
-    if (i >= A.n) return;            // zero-mass pads stay at rest at the origin (packed once at upload)
-    double4 p = A.pos[i], v = A.vel[i];
-    if (subtract_com) {
-        const double M = A.red[3];
-        const double inv = M != 0.0 ? 1.0 / M : 0.0;
-        v.x -= A.red[0] * inv; v.y -= A.red[1] * inv; v.z -= A.red[2] * inv;
+    const long i = A.i0 + (long)blockIdx.x * kThreads + threadIdx.x;
+    double4 p = A.pos[i];
+    const bool real = i < A.n;       // zero-mass pads stay at rest where they were put at upload
+    if (real) {
+        double4 v = A.vel[i];
+        if (subtract_com) {
+            const double M = A.red[3];
+            const double inv = M != 0.0 ? 1.0 / M : 0.0;
+            v.x -= A.red[0] * inv; v.y -= A.red[1] * inv; v.z -= A.red[2] * inv;
+        }
+        const double ax = A.acc[i], ay = A.acc[A.npad + i], az = A.acc[2 * A.npad + i];
+        if (INTEG == NB_INTEG_VELOCITY_VERLET) {
+            // cuda/IntegrationKernels.cu:36-38 ; core/System.cpp:463-465
+            p.x += v.x * dt + 0.5 * ax * (dt * dt);
+            p.y += v.y * dt + 0.5 * ay * (dt * dt);
+            p.z += v.z * dt + 0.5 * az * (dt * dt);
+            if (subtract_com) A.vel[i] = v;
+        } else {
+            // cuda/IntegrationKernels.cu:74-81 ; core/System.cpp:417-424: x uses the old v, then v += a dt
+            p.x += v.x * dt; p.y += v.y * dt; p.z += v.z * dt;
+            v.x += ax * dt; v.y += ay * dt; v.z += az * dt;
+            A.vel[i] = v;
+        }
+        A.pos[i] = p;
+        if (A.pk) pack_one(A.pk, i, p, inv3mbar);
     }
-    const double ax = A.acc[i], ay = A.acc[A.npad + i], az = A.acc[2 * A.npad + i];
-    if (INTEG == NB_INTEG_VELOCITY_VERLET) {
-        // cuda/IntegrationKernels.cu:36-38 ; core/System.cpp:463-465
-        p.x += v.x * dt + 0.5 * ax * (dt * dt);
-        p.y += v.y * dt + 0.5 * ay * (dt * dt);
-        p.z += v.z * dt + 0.5 * az * (dt * dt);
-        if (subtract_com) A.vel[i] = v;
-    } else {
-        // cuda/IntegrationKernels.cu:74-81 ; core/System.cpp:417-424: x uses the old v, then v += a dt
-        p.x += v.x * dt; p.y += v.y * dt; p.z += v.z * dt;
-        v.x += ax * dt; v.y += ay * dt; v.z += az * dt;
-        A.vel[i] = v;
-    }
-    A.pos[i] = p;
-    if (A.pk) pack_one(A.pk, i, p, inv3mbar);
+    if (A.pk) tile_meta(A.pk, i / kTJ, (float)p.x, (float)p.y, (float)p.z);
 }
 
 // finish: reduce the force partials in slot order; VV kick; per-block sums of (m vx, m vy, m vz, m).
@@ -205,6 +232,7 @@ inline unsigned blocks_for(long count) { return (unsigned)((count + kThreads - 1
 
 int launch_pack(const StepArrays& A, long first, long count, double avg_mass, cudaStream_t st) {
     if (count <= 0 || !A.pk) return NB_OK;
+    if (first % kTJ || count % kTJ) return fail(NB_ERR_INVALID, "pack: range [%ld,+%ld) is not tile aligned", first, count);
     const double inv3mbar = avg_mass > 0.0 ? 1.0 / (3.0 * avg_mass) : 0.0;
     pack_kernel<<<blocks_for(count), kThreads, 0, st>>>(A.pos, A.pk, first, count, inv3mbar);
     NB_CUDA(cudaGetLastError());
