@@ -145,6 +145,23 @@ int nb_run_simulation(long n, double* posMass4, double* vel4, int integration_me
 int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, double* d_accel4,
                     double avg_mass, long n, void* stream);
 
+/* ---- allocation-free force evaluation ---------------------------------------------------------------------------------
+ * No counterpart in the reference (its drivers cudaMalloc on every call). One force evaluation a = F(x) on caller-owned
+ * device arrays (n x double4 in, n x double4 (ax,ay,az,0) out, caller's particle order) that performs no device or
+ * pinned allocation at all: the packed tiles and partial sums live in a fixed ~7.5 MB block of device memory built into
+ * the library (held by every GPU that loads it, until the process exits). For callers that must not allocate after
+ * start-up: plug-ins inside an application whose own pool already owns the device memory (cudaMalloc would fail),
+ * per-frame / per-step loops that cannot take cudaMalloc's device-wide synchronisation, jobs with a fixed, declared
+ * memory footprint. Limits and rules:
+ *   - n <= NB_NOALLOC_MAX_N, otherwise NB_ERR_INVALID with an explanatory message; FP32 pair math (<= 1e-5);
+ *   - ADAPTIVE_MUTUAL needs avg_mass > 0 (the mean mass, as the reference's launchForceKernel takes it);
+ *   - asynchronous on `stream` (cudaStream_t; NULL = default stream); the device current at the call is used;
+ *   - the first call on each device resolves the block's device address; issue it during start-up, before any stream
+ *     capture begins;
+ *   - all calls on a device share the block: calls that overlap on the GPU race — keep them on one stream. */
+#define NB_NOALLOC_MAX_N 32768
+int nb_force_noalloc(int force_method, const double* d_posMass4, double* d_accel4, long n, double avg_mass, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -234,6 +234,7 @@ def test_launch_force_on_caller_device_arrays(lib, oracle):
     d_pos = torch.from_numpy(pm).cuda()
     d_acc = torch.zeros_like(d_pos)
     stream = torch.cuda.Stream()
+    torch.cuda.synchronize()
     with lib.context(5000, FP32) as ctx:
         with torch.cuda.stream(stream):
             for force in (PAIRWISE, ADAPTIVE):
