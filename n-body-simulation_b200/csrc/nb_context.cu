@@ -151,13 +151,18 @@ int check_force_method(int force) {
 
 int splits_for(nb_ctx* c, int iblocks, int jcount) {
     if (c->j_splits > 0) return c->j_splits < jcount ? c->j_splits : jcount;
-    // enough CTAs for >= 4 full waves of 148 SMs x 2 resident CTAs, so the tail wave costs little
-    const int target = 148 * 2 * 4;
-    int S = (target + iblocks - 1) / iblocks;
-    if (S > 32) S = 32;
-    if (S > jcount) S = jcount;
-    if (S < 1) S = 1;
-    return S;
+    // All CTAs of a launch do the same amount of work (jcount / S tiles for 512 i-particles), so the launch runs in
+    // ceil(CTAs / 296) waves of 148 SMs x 2 resident CTAs. Pick the S whose last wave is fullest, among those that give
+    // at least ~4 waves; ties go to the smaller S (less partial-sum traffic).
+    const double slots = 148.0 * 2.0;
+    int best = 1; double best_eff = -1.0;
+    for (int S = 1; S <= 32 && S <= jcount; ++S) {
+        const double waves = (double)iblocks * S / slots;
+        double eff = waves / (double)(long)(waves + 0.999999);
+        if (waves < 4.0) eff *= 0.5 + waves / 8.0;          // too few waves: prologue/tail dominate, keep splitting
+        if (eff > best_eff * 1.015) { best_eff = eff; best = S; }
+    }
+    return best;
 }
 
 int ensure_part(nb_ctx* c, int S_total) {
@@ -198,9 +203,8 @@ int eval_force(nb_ctx* c, int* S_out) {
         rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
         *S_out = L.S;
     } else {
-        const int St = splits_for(c, iblocks, c->ntiles);
-        int SA = St / c->world; if (SA < 1) SA = 1; if (SA > nit) SA = nit;
-        int SB = St - SA; if (SB < 1) SB = 1; if (SB > c->ntiles - nit) SB = c->ntiles - nit;
+        const int SA = splits_for(c, iblocks, nit);
+        const int SB = splits_for(c, iblocks, c->ntiles - nit);
         int rc = ensure_part(c, SA + SB); if (rc) return rc;
         L.jt0 = it0; L.jcount = nit; L.s0 = 0; L.S = SA;
         rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
