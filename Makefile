@@ -9,8 +9,8 @@ NVFLAGS:= $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Iinclude -I$(CSRC) 
 CU_SRCS := $(CSRC)/nb_force.cu $(CSRC)/nb_integrate.cu $(CSRC)/nb_sort.cu $(CSRC)/nb_context.cu $(CSRC)/nb_noalloc.cu
 CU_OBJS := $(CU_SRCS:.cu=.o)
 
-.PHONY: all lib oracle ref tools host clean
-all: lib oracle ref tools host
+.PHONY: all lib oracle ref refgpu tools host clean
+all: lib oracle ref tools host refgpu
 
 lib: $(LIB)
 $(CSRC)/%.o: $(CSRC)/%.cu $(CSRC)/nb_common.cuh include/nbody_b200.h
@@ -22,13 +22,15 @@ oracle:
 	$(MAKE) -C oracle oracle
 ref:
 	$(MAKE) -C oracle ref
+refgpu: lib
+	$(MAKE) -C oracle refgpu
 
 tools: tools/pipe_bench
 tools/pipe_bench: tools/pipe_bench.cu
 	$(NVCC) $(ARCH) -O3 -std=c++17 -lineinfo -o $@ $<
 
-host:
-	@if [ -f host/Makefile ]; then $(MAKE) -C host; fi
+host: lib
+	$(MAKE) -C host
 
 clean:
 	rm -f $(CSRC)/*.o $(CSRC)/*.ptxas.log $(LIB) tools/pipe_bench

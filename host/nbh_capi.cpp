@@ -1,0 +1,47 @@
+// nbh_capi.cpp — plain-C exports of the host layer (libnbody_host.so) so that tests and bench.py can call the C++
+// generators / config parser / run driver through ctypes. All functions return 0 on success; nbh_last_error() has the text.
+#include <cstring>
+#include <string>
+
+#include "nbh_host.hpp"
+
+namespace { thread_local std::string g_err; 
+int fill(const nbh::InitResult& r, long cap, long* n_out, double* posMass4, double* vel4, char* meta, long meta_cap) {
+    *n_out = (long)r.particles.n;
+    const long n = (long)r.particles.n < cap ? (long)r.particles.n : cap;
+    std::memcpy(posMass4, r.particles.posMass.data(), (size_t)n * 32);
+    std::memcpy(vel4, r.particles.vel.data(), (size_t)n * 32);
+    if (meta && meta_cap > 0) { std::strncpy(meta, r.metadata.c_str(), (size_t)meta_cap - 1); meta[meta_cap - 1] = 0; }
+    return 0;
+}
+template <typename F> int guard(F f) { try { return f(); } catch (const std::exception& e) { g_err = e.what(); return 1; } } }
+
+extern "C" {
+const char* nbh_last_error(void) { return g_err.c_str(); }
+
+// Initial conditions from a config.json text (the "init" block + optional "seed"); cap = rows available in the outputs.
+int nbh_init_from_config(const char* config_text, long cap, long* n_out, double* posMass4, double* vel4, char* meta, long meta_cap) {
+    return guard([&] { nbh::Config c = nbh::parse_config_text(config_text);
+                       return fill(nbh::create_initial_conditions(c), cap, n_out, posMass4, vel4, meta, meta_cap); });
+}
+int nbh_init_spiral(int nStars, double totalMass, int nArms, double radius, double thickness, double perturbation,
+                    unsigned long seed, long cap, long* n_out, double* posMass4, double* vel4) {
+    return guard([&] { return fill(nbh::init_spiral_galaxy(nStars, totalMass, nArms, radius, thickness, perturbation, &seed), cap, n_out, posMass4, vel4, nullptr, 0); });
+}
+int nbh_init_random(int n, double minMass, double maxMass, double L, double maxVel, double minDist, unsigned long seed,
+                    long cap, long* n_out, double* posMass4, double* vel4) {
+    return guard([&] { return fill(nbh::init_random(n, minMass, maxMass, L, maxVel, minDist, &seed), cap, n_out, posMass4, vel4, nullptr, 0); });
+}
+// Parse + validate only: fills steps, stepFreq and the enum values. out[0..7] = steps, stepFreq, integ, force, exec, output, threads, hasSeed
+int nbh_parse_config(const char* config_text, long out[8]) {
+    return guard([&] { nbh::Config c = nbh::parse_config_text(config_text);
+                       const long steps = (long)(c.years / c.dtYears);
+                       out[0] = steps; out[1] = steps / 500 > 1 ? steps / 500 : 1; out[2] = (long)c.integrationMethod; out[3] = (long)c.forceMethod;
+                       out[4] = (long)c.executionMode; out[5] = (long)c.outputMode; out[6] = c.threads; out[7] = c.hasSeed ? 1 : 0; return 0; });
+}
+// Whole run of a config text through the C ABI of libnbody_b200 (BENCHMARK or FILE_CSV).
+int nbh_run_config(const char* config_text, double* run_seconds, long* n_out, long* steps_out) {
+    return guard([&] { nbh::Config c = nbh::parse_config_text(config_text); nbh::RunReport r = nbh::run_config(c, true);
+                       if (run_seconds) *run_seconds = r.run_seconds; if (n_out) *n_out = (long)r.n; if (steps_out) *steps_out = r.steps; return 0; });
+}
+}

@@ -1,0 +1,190 @@
+"""The C++17 host drop-in (host/): config.json surface, generators, BENCHMARK / FILE_CSV sinks, and the reference's own
+System.cpp linked against host/ref_shims.cpp. CPU tests need no GPU; the gpu-marked ones run the binaries on the box."""
+import ctypes as C
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import nbtest
+
+PKG = os.path.join(nbtest.ROOT, "n-body-simulation_b200")
+HOST_LIB = os.path.join(PKG, "libnbody_host.so")
+HOST_BIN = os.path.join(PKG, "nbody_host")
+REF_BIN = os.path.join(nbtest.ROOT, "oracle", "_ref", "ref_system_on_b200")
+
+BASE = {
+    "init": {
+        "selected": "RANDOM",
+        "FROM_FILE": {"filePath": os.path.join(nbtest.ROOT, "data_in", "sistema.dat"), "partialCount": 25},
+        "RANDOM": {"nParticles": 600, "minMass": 1e-10, "maxMass": 1e-5, "L": 1e2, "maxVelocity": 1.0, "minDistance": 1e-3},
+        "GALAXY": {"nStars": 100, "blackHoleMass": 4e6, "starMassMin": 0.1, "starMassMax": 10.0, "maxPosition": 330000,
+                   "maxVelocity": 42.15, "addPlanets": True, "minPlanets": 2, "maxPlanets": 2, "planetMassMin": 1.7e-7,
+                   "planetMassMax": 9.6e-4, "planetDistanceMax": 6.68, "planetVelocityMax": 6.32},
+        "STELLAR_SYSTEM": {"nPlanets": 50, "starMass": 1.0, "planetMassMin": 1.7e-8, "planetMassMax": 9.6e-4,
+                           "minPlanetDistance": 0.73, "maxPlanetDistance": 16.68, "addMoons": True, "minMoons": 1, "maxMoons": 3,
+                           "moonMassMin": 5e-10, "moonMassMax": 5e-8, "moonDistanceMax": 0.00067, "moonVelocityMax": 0.211},
+        "SPIRAL_GALAXY": {"nStars": 5000, "totalMass": 1e4, "nArms": 2, "galaxyRadius": 3.09398e3, "thickness": 6.18795e2,
+                          "perturbation": 5.0},
+    },
+    "threads": 2, "years": 100.0, "dtYears": 4e-2, "output": {"dir": "", "file": "out.csv"},
+    "integrationMethod": "VELOCITY_VERLET", "forceMethod": "PAIRWISE", "executionMode": "GPU", "outputMode": "BENCHMARK",
+}
+
+
+def cfg_text(**over):
+    c = json.loads(json.dumps(BASE))
+    for k, v in over.items():
+        if k == "selected":
+            c["init"]["selected"] = v
+        else:
+            c[k] = v
+    # the reference's shipped file has comment lines after the closing brace (config.json:67-68)
+    return json.dumps(c, indent=1) + "\n# trailing comment line, tolerated like the reference's `in >> j`\n"
+
+
+@pytest.fixture(scope="module")
+def host():
+    l = C.CDLL(HOST_LIB)
+    l.nbh_last_error.restype = C.c_char_p
+    l.nbh_init_from_config.argtypes = [C.c_char_p, C.c_long, C.POINTER(C.c_long), nbtest._dp, nbtest._dp, C.c_char_p, C.c_long]
+    l.nbh_parse_config.argtypes = [C.c_char_p, C.POINTER(C.c_long)]
+    return l
+
+
+def init_from(host, text, cap=400000):
+    pm = np.zeros((cap, 4)); v = np.zeros((cap, 4)); n = C.c_long(0); meta = C.create_string_buffer(4096)
+    rc = host.nbh_init_from_config(text.encode(), cap, C.byref(n), pm.ctypes.data_as(nbtest._dp), v.ctypes.data_as(nbtest._dp),
+                                   meta, 4096)
+    if rc != 0:
+        raise RuntimeError(host.nbh_last_error().decode())
+    return pm[:n.value].copy(), v[:n.value].copy(), meta.value.decode()
+
+
+def test_config_surface(host):
+    out = (C.c_long * 8)()
+    assert host.nbh_parse_config(cfg_text().encode(), out) == 0, host.nbh_last_error()
+    assert list(out) == [2500, 5, 1, 0, 1, 0, 2, 0]           # steps = years/dt (main.cpp:496), stepFreq = max(1, n/500)
+    assert host.nbh_parse_config(cfg_text(forceMethod="ADAPTIVE_MUTUAL", integrationMethod="EULER", outputMode="FILE_CSV",
+                                          executionMode="CPU", seed=7).encode(), out) == 0
+    assert list(out)[2:6] == [0, 2, 0, 1] and out[7] == 1
+    for key, bad, msg in (("forceMethod", "FAST", "Unknown force method: FAST"),
+                          ("integrationMethod", "RK4", "Unknown integration method: RK4"),
+                          ("executionMode", "TPU", "Unknown execution mode: TPU"),
+                          ("outputMode", "PNG", "Unknown output mode: PNG")):
+        assert host.nbh_parse_config(cfg_text(**{key: bad}).encode(), out) == 1
+        assert host.nbh_last_error().decode() == msg
+    assert host.nbh_parse_config(b'{"init": {"selected": "RANDOM"}}', out) == 1
+    assert "missing key" in host.nbh_last_error().decode()
+    assert host.nbh_parse_config(b'{"init": ', out) == 1
+
+
+def test_generators_are_seeded_and_shaped(host):
+    a = init_from(host, cfg_text(seed=5))
+    b = init_from(host, cfg_text(seed=5))
+    c = init_from(host, cfg_text(seed=6))
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and not np.array_equal(a[0], c[0])
+    pm, v, meta = a
+    assert pm.shape == (600, 4) and "# Number of particles: 600" in meta and "# Total particle count: 600" in meta
+    assert np.abs(pm[:, :3]).max() <= 50 and np.abs(v[:, :3]).max() <= 1 and np.all(v[:, 3] == 0)
+    assert pm[:, 3].min() >= 1e-10 and pm[:, 3].max() <= 1e-5
+    d = np.linalg.norm(pm[:, None, :3] - pm[None, :, :3], axis=2) + np.eye(600) * 1e9
+    assert d.min() >= 1e-3                                      # minDistance honoured
+
+    pm, v, meta = init_from(host, cfg_text(selected="GALAXY", seed=1))
+    assert pm.shape[0] == 1 + 100 * 3 and pm[0, 3] == 4e6 and np.all(pm[0, :3] == 0)   # min = max = 2 planets per star
+    stars, p1 = pm[1::3], pm[2::3]
+    assert np.abs(p1[:, :3] - stars[:, :3]).max() <= 6.68 and p1[:, 3].max() <= 9.6e-4 and stars[:, 3].min() >= 0.1
+
+    pm, v, meta = init_from(host, cfg_text(selected="SPIRAL_GALAXY", seed=1))
+    assert pm.shape[0] == 5000 and np.allclose(pm[:, 3], 1e4 / 5000)
+    assert np.linalg.norm(pm[:, :3], axis=1).max() <= np.hypot(3.09398e3, 6.18795e2 / 2) * 1.0001
+    assert "# Initializer: Spiral Galaxy" in meta
+
+    pm, v, meta = init_from(host, cfg_text(selected="STELLAR_SYSTEM", seed=1))
+    assert pm[0, 3] == 1.0 and np.all(pm[:, 2] == 0)            # everything in the XY plane
+    assert 1 + 50 * 2 <= pm.shape[0] <= 1 + 50 * 4
+    # config passes moonDistanceMax / moonVelocityMax into the (min, max) moon-distance slots (ConfigParser.hpp:146-152)
+    assert "# moonDistance range: [0.00067, 0.211] AU" in meta
+
+    pm, v, meta = init_from(host, cfg_text(selected="FROM_FILE"))
+    ref_pm, ref_v = nbtest.load_sistema()
+    np.testing.assert_allclose(pm, ref_pm, rtol=1e-15); np.testing.assert_allclose(v, ref_v, rtol=1e-15)
+    assert "# Total in file: 25" in meta
+
+
+def test_host_generators_match_reference_distributions(host, ref):
+    pm, v, _ = init_from(host, cfg_text(selected="SPIRAL_GALAXY", seed=3))
+    rp, rv = ref.init_spiral(5000)
+    for a, b in ((pm, rp), (v, rv)):
+        ra, rb = np.linalg.norm(a[:, :3], axis=1), np.linalg.norm(b[:, :3], axis=1)
+        assert abs(ra.mean() - rb.mean()) < 0.05 * rb.mean() and abs(ra.std() - rb.std()) < 0.08 * rb.std()
+    pm, v, _ = init_from(host, cfg_text(seed=3))
+    rp, rv = ref.init_random(600)
+    assert abs(pm[:, 3].mean() - rp[:, 3].mean()) < 0.15 * rp[:, 3].mean()
+    assert abs(np.abs(v[:, :3]).mean() - np.abs(rv[:, :3]).mean()) < 0.1
+
+
+def test_host_binary_fails_loudly_without_gpu(tmp_path, lib):
+    if lib.l.nb_device_count() > 0:
+        pytest.skip("a GPU is present")
+    (tmp_path / "config.json").write_text(cfg_text(seed=1))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 1 and "no CUDA device" in r.stderr
+    (tmp_path / "config.json").write_text(cfg_text(executionMode="CPU"))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 1 and "no CPU fallback" in r.stderr
+    (tmp_path / "config.json").write_text(cfg_text(outputMode="VISUALIZATION"))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True)
+    assert r.returncode == 1 and "reference-only" in r.stderr
+
+
+@pytest.mark.gpu
+def test_host_benchmark_mode(tmp_path):
+    (tmp_path / "config.json").write_text(cfg_text(seed=1, years=0.4, dtYears=0.04))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Simulation time:" in r.stdout and "(using GPU)" in r.stdout and "Force method: Pairwise" in r.stdout
+    (tmp_path / "config.json").write_text(cfg_text(seed=1, forceMethod="BARNES_HUT"))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 1 and "reference-only" in r.stderr
+
+
+@pytest.mark.gpu
+def test_host_file_csv_mode(tmp_path, host, oracle):
+    text = cfg_text(seed=2, years=1.0, dtYears=0.01, outputMode="FILE_CSV", forceMethod="ADAPTIVE_MUTUAL")
+    text = text.replace('"nParticles": 600', '"nParticles": 40')
+    (tmp_path / "config.json").write_text(text)
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    lines = (tmp_path / "out.csv").read_text().splitlines()
+    hdr = lines.index("particle_id,time,x,y,z,vx,vy,vz,mass,energy")
+    assert lines[0].startswith("# years: 1.0") and any(l == "# force method: Adaptive Mutual" for l in lines[:hdr])
+    rows = [l.split(",") for l in lines[hdr + 1:]]
+    assert len(rows) == 101 * 40                                # steps=100, stepFreq=1 -> 101 snapshots
+    pm, v, _ = init_from(host, text)
+    first = np.array(rows[:40], dtype=float)
+    np.testing.assert_allclose(first[:, 2:5], pm[:, :3], atol=6e-9)
+    np.testing.assert_allclose(first[:, 8], pm[:, 3], atol=6e-9)
+    assert first[0, 0] == 0 and first[39, 0] == 39 and float(rows[40][1]) == pytest.approx(0.01)
+    assert float(rows[0][9]) == pytest.approx(oracle.energy(pm, v), rel=1e-9)
+    p_end, v_end = oracle.step(pm, v, nbtest.VV, nbtest.ADAPTIVE, 0.01, 100)
+    last = np.array(rows[-40:], dtype=float)
+    np.testing.assert_allclose(last[:, 2:5], p_end[:, :3], atol=2e-7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("prec,tol", [("0", 2e-5), ("1", 1e-9)], ids=["fp32", "fp64"])
+def test_reference_system_cpp_runs_on_the_b200_library(prec, tol):
+    """The reference's own System.cpp/Forces.cpp, linked with host/ref_shims.cpp: System(GPU).runBenchmark goes through
+    runBenchmarkOnGPU -> nb_run_benchmark and lands on the same state as the reference's CPU/OpenMP run."""
+    if not os.path.exists(REF_BIN):
+        pytest.skip("oracle/_ref/ref_system_on_b200 not built (reference tree absent at build time)")
+    env = dict(os.environ, NB_PRECISION=prec, OMP_NUM_THREADS="8")
+    r = subprocess.run([REF_BIN, "1500", "10", "0.01", "0", "1"], capture_output=True, text=True, env=env, timeout=300)
+    assert r.returncode == 0, r.stderr
+    d = json.loads(r.stdout.strip().splitlines()[-1])
+    assert d["n"] == 1500 and d["max_abs_dpos"] <= tol * 50 and d["max_abs_dvel"] <= tol * 50
+    assert abs(d["E_gpu"] - d["E_cpu"]) <= 1e-6 * abs(d["E_cpu"])
