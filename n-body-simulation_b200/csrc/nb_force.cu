@@ -362,6 +362,29 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
 // ------------------------------------------------------------------------------------------------------------------
 // FP64 mode. Tiles of 256 double4 (x,y,z,m) straight from the master array; R = 2 i-particles per thread.
 constexpr int kR64 = 2;
+
+__device__ __forceinline__ double rsq64_seed(double x) { double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y; }
+
+// gm * s2^(-3/2) to full double precision without the branches of the library rsqrt(): seed y0 from MUFU.RSQ64H
+// (~1e-6), e = 1 - s2 y0^2, then s2^(-3/2) = y0^3 (1 + 3/2 e + 15/8 e^2 + O(e^3)). 7 DP operations.
+__device__ __forceinline__ double gm_inv_r3(double s2, double gm) {
+    const double y0 = rsq64_seed(s2);
+    const double t = y0 * y0;
+    const double e = fma(s2, -t, 1.0);
+    const double sc0 = (gm * y0) * t;
+    const double c = e * fma(e, 1.875, 1.5);
+    return fma(sc0, c, sc0);
+}
+// q^(2/3) for q >= 0: y0 ~ q^(-1/3) from the FP32 MUFU (lg2/ex2), one Newton step for y = q^(-1/3) in double
+// (y1 = y0 (4 - q y0^3) / 3, error ~2e-12 relative), q^(2/3) = q y1. Replaces cbrt() of core/Forces.cpp:354.
+__device__ __forceinline__ double pow23(double q) {
+    const float qf = fmaxf((float)q, 1e-30f);
+    const double y0 = (double)ex2_approx(lg2_approx(qf) * -0.3333333333333333f);
+    const double a = q * y0;
+    const double b = a * (y0 * y0);
+    return a * fma(b, -0.3333333333333333, 1.3333333333333333);
+}
+
 template <bool ADAPTIVE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, const ForceLaunch L, double inv3mbar) {
@@ -369,11 +392,11 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
     const int t = threadIdx.x, s = blockIdx.y;
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
     const int itile_first = L.it0 + blockIdx.x * kR64;
-    double xi[kR64], yi[kR64], zi[kR64], mi[kR64], ax[kR64], ay[kR64], az[kR64];
+    double xi[kR64], yi[kR64], zi[kR64], mqi[kR64], ax[kR64], ay[kR64], az[kR64];
 #pragma unroll
     for (int r = 0; r < kR64; ++r) {
         const double4 p = pos[(size_t)(itile_first + r) * kTJ + t];
-        xi[r] = p.x; yi[r] = p.y; zi[r] = p.z; mi[r] = p.w; ax[r] = ay[r] = az[r] = 0.0;
+        xi[r] = p.x; yi[r] = p.y; zi[r] = p.z; mqi[r] = p.w * inv3mbar; ax[r] = ay[r] = az[r] = 0.0;
     }
     double4 g = make_double4(0, 0, 0, 0);
     if (k0 < k1) sm[0][t] = pos[(size_t)wrap_tile(L.jt0 + k0, L.ntiles) * kTJ + t];
@@ -385,19 +408,23 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
 #pragma unroll 4
         for (int j = 0; j < kTJ; ++j) {
             const double4 pj = sm[b][j];
+            const double gm = kG * pj.w;
+            const double mqj = ADAPTIVE ? pj.w * inv3mbar : 0.0;
 #pragma unroll
             for (int r = 0; r < kR64; ++r) {
                 const double dx = pj.x - xi[r], dy = pj.y - yi[r], dz = pj.z - zi[r];
                 const double r2 = dx * dx + dy * dy + dz * dz;
                 double s2 = r2;
                 if (ADAPTIVE) {
-                    const double c = cbrt((mi[r] + pj.w) * inv3mbar);
-                    s2 = fmax(r2 + 1e-4 * r2 * (c * c), r2 + 1e-8);
+                    // eps^2 = max(eta^2 r^2 q^(2/3), eps_min^2) (core/Forces.cpp:353-356)
+                    const double w = pow23(mqi[r] + mqj);
+                    s2 = fmax(fma(r2 * w, 1e-4, r2), r2 + 1e-8);
                 }
-                double ri = rsqrt(s2);
-                ri = r2 < kR2Cut ? 0.0 : ri;
-                const double sc = (kG * pj.w) * ri * (ri * ri);
-                ax[r] += sc * dx; ay[r] += sc * dy; az[r] += sc * dz;
+                double sc = gm_inv_r3(s2, gm);
+                // r2 >= 0, so the integer order of the bit patterns is the floating-point order: the cut-off test
+                // (core/Forces.cpp:144) runs on the integer pipe instead of the FP64 pipe.
+                sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;
+                ax[r] = fma(sc, dx, ax[r]); ay[r] = fma(sc, dy, ay[r]); az[r] = fma(sc, dz, az[r]);
             }
         }
         if (more) sm[b ^ 1][t] = g;
