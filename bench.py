@@ -85,6 +85,22 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def ncu_traffic_bytes(n, force, prec, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum per force-kernel launch from the committed `ncu --set full` capture
+    (profiles/), valid for the default workload only; None otherwise."""
+    if not (n == 1048576 and force == nbtest.PAIRWISE and prec == nbtest.FP32 and world == 1):
+        return None
+    path = os.path.join(ROOT, "profiles", "r01_ncu_force_fp32_tma_frame_kernel.txt")
+    try:
+        tot = 0.0
+        for line in open(path):
+            if line.startswith("dram__bytes_read.sum [Mbyte]") or line.startswith("dram__bytes_write.sum [Mbyte]"):
+                tot += float(line.split("=")[1]) * 1e6
+        return tot or None
+    except OSError:
+        return None
+
+
 def pinned(n_rows):
     import torch
     t = torch.empty((n_rows, 4), dtype=torch.float64).pin_memory()
@@ -155,7 +171,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=1048576, help="particles (SPIRAL_GALAXY)")
+    ap.add_argument("--particles", "--n", dest="n", type=int, default=1048576, help="particles (SPIRAL_GALAXY); use --particles under torchrun (its parser treats --n as ambiguous)")
     ap.add_argument("--force", default="PAIRWISE", choices=["PAIRWISE", "ADAPTIVE_MUTUAL"])
     ap.add_argument("--precision", default="fp32", choices=["fp32", "fp64"])
     ap.add_argument("--variant", type=int, default=0, help="force kernel tile staging: 0 auto, 1 loads, 2 bulk copy")
@@ -280,7 +296,9 @@ def main():
         roofline = {"bound": "fp32-issue (not hbm, not tensor: 13 FP32-pipe slots + 1 MUFU per interaction, SURVEY.md 8d)",
                     "achieved": ach_int * SLOTS_PER_INTERACTION * 2 / 1e12,
                     "peak": peak_int * SLOTS_PER_INTERACTION * 2 / 1e12, "unit": "TFLOP/s",
-                    "frac": ach_int / peak_int, "traffic": None,
+                    "frac": ach_int / peak_int, "traffic": ncu_traffic_bytes(n, force, prec, world),
+                    "traffic_note": "DRAM bytes per launch from profiles/r01_ncu_force_fp32_tma_frame_kernel.txt; the "
+                                    "kernel's operands are 37.7 MB of packed tiles re-read from L2 by every CTA",
                     "achieved_Tint_per_s": ach_int / 1e12, "peak_Tint_per_s": peak_int / 1e12,
                     "kernel": "force_fp32 (per-GPU launch time from CUDA events on the context stream)",
                     "kernel_ms": fk_ms, "share_of_step": fk_ms / (t_step * 1e3),

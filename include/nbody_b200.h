@@ -36,7 +36,7 @@ extern "C" {
 #define NB_FORCE_ADAPTIVE_MUTUAL     2
 #define NB_FORCE_BARNES_HUT          3   /* reference-only: NB_ERR_UNSUPPORTED */
 /* Arithmetic of the pair loop (new, optional; the reference GPU path is FP64 only) */
-#define NB_PREC_FP32   0   /* two-float (hi+lo) positions, FP32 pair math, FP64 accumulation across j-tiles; <=1e-5 */
+#define NB_PREC_FP32   0   /* two-float positions; FP32 pair math for far tiles, FP64 for adjacent tiles, FP64 sums; <=1e-5 */
 #define NB_PREC_FP64   1   /* FP64 pair math throughout; <=1e-12                                                    */
 
 typedef struct nb_ctx nb_ctx;
@@ -115,12 +115,14 @@ int nb_force_timing(nb_ctx* ctx, int reset, float* mean_ms, int* evals);
 int nb_timer_start(nb_ctx* ctx);
 int nb_timer_stop(nb_ctx* ctx, float* ms);
 /* Tuning knobs (optional; set before nb_upload):
- *   "force_variant"    0 auto (= 2) | 1 plain-load tiles, global hi+lo coordinates for every tile (simple, slower)
- *                      | 2 bulk-copy (TMA) tiles re-expressed in the i-block's own frame, far tiles hi-only
+ *   "force_variant"    0 auto (= 3)
+ *                      | 1 plain-load tiles, global two-float coordinates for every tile (simple cross-check)
+ *                      | 2 bulk-copy (TMA) tiles in the i-block's frame, 2 i-particles/thread, FP32 two-float near field
+ *                      | 3 as 2 with 4 i-particles/thread and the near field (adjacent tiles) in FP64 (production)
  *   "j_splits"         0 auto | 1..64 CTAs sharing one i-block's j-range
  *   "spatial_sort"     1 (default) Morton-order the particles at upload | 0 keep the caller's order
  *   "far_kappa_milli"  1000*kappa of the far-tile criterion box gap > kappa*(half-extent_i + half-extent_j)
- *                      (default 1000); 0 = always use the accurate two-float path */
+ *                      (default 250); 0 = every tile through the near-field path */
 int nb_set_option(nb_ctx* ctx, const char* key, long value);
 
 /* ---- whole-run entry points with HOST buffers: what the reference's host code binds ------------------------------ */
@@ -148,7 +150,7 @@ int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, dou
 /* ---- allocation-free force evaluation ---------------------------------------------------------------------------------
  * No counterpart in the reference (its drivers cudaMalloc on every call). One force evaluation a = F(x) on caller-owned
  * device arrays (n x double4 in, n x double4 (ax,ay,az,0) out, caller's particle order) that performs no device or
- * pinned allocation at all: the packed tiles and partial sums live in a fixed ~7.5 MB block of device memory built into
+ * pinned allocation at all: the packed tiles and partial sums live in a fixed ~7.6 MB block of device memory built into
  * the library (held by every GPU that loads it, until the process exits). For callers that must not allocate after
  * start-up: plug-ins inside an application whose own pool already owns the device memory (cudaMalloc would fail),
  * per-frame / per-step loops that cannot take cudaMalloc's device-wide synchronisation, jobs with a fixed, declared

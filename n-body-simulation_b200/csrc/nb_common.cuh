@@ -29,9 +29,11 @@ constexpr double kR2Cut    = 1e-10;   // core/Forces.cpp:144,350 — pairs with 
 //   row 8     meta       [0..2] bbox min, [3..5] bbox max of the tile's hi positions, [6] max |coordinate|; rest unused.
 //                        Travels with the tile (bulk copy, all-gather) so the kernel can pick the cheap path per tile.
 constexpr int kTJ = 256;                 // j-particles per tile == threads per CTA
-constexpr int kNC = 9;                   // rows per tile
+//   row 9     gml        (float)(G m - (double)gm): low part of G m for the FP64 near-field path
+constexpr int kNC = 10;                  // rows per tile
 constexpr int kMetaRow = 8;
-constexpr int kTileFloats = kTJ * kNC;   // 2304 floats = 9216 bytes
+constexpr int kGmLoRow = 9;
+constexpr int kTileFloats = kTJ * kNC;   // 2560 floats = 10240 bytes
 constexpr int kTileBytes  = kTileFloats * 4;
 constexpr int kAlign = 1024;             // particle counts are padded to a multiple of this (4 tiles)
 constexpr int kThreads = 256;
@@ -42,6 +44,7 @@ struct ForceLaunch {          // one launch = i-tiles [it0, it0+nit) against the
     int ntiles;               // tiles in the whole padded system
     long npad;                // padded particle count (row stride of `part`)
     int s0, S;                // this launch writes partial slots s0 .. s0+S-1
+    float g0;                 // mass scale G * (mean mass) of the mass-scaled far path (> 0)
     float kappa;              // far-tile criterion: box gap > kappa * (|x|max_i + |x|max_j); huge = always accurate path
 };
 
@@ -56,6 +59,7 @@ int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, bool 
 int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, bool adaptive, double avg_mass, cudaStream_t st);
 int launch_potential_fp64(const double4* pos, double* pot, long npad, int ntiles, cudaStream_t st);
 int force_regs_info(char* buf, int len);
+int force_i_tiles_per_cta(int variant);
 
 // nb_integrate.cu
 struct StepArrays {

@@ -73,7 +73,7 @@ struct nb_ctx {
     double4 *pos = nullptr, *vel = nullptr, *tmp4 = nullptr, *stage_pos = nullptr, *stage_vel = nullptr;
     unsigned int* perm = nullptr;          // perm[sorted slot] = caller index
     SortScratch ss;
-    int spatial_sort = 1; float kappa = 1.0f;
+    int spatial_sort = 1; float kappa = 0.25f;
     double *acc = nullptr, *part = nullptr, *red_part = nullptr, *red = nullptr, *eout = nullptr;
     float* pk = nullptr;
     size_t part_bytes = 0;
@@ -178,7 +178,7 @@ int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const 
     const bool adaptive = (c->force == NB_FORCE_ADAPTIVE_MUTUAL);
     int rc;
     if (c->precision == NB_PREC_FP32) {
-        const int variant = c->force_variant == 0 ? 2 : c->force_variant;
+        const int variant = c->force_variant == 0 ? 3 : c->force_variant;
         rc = launch_force_fp32(pk, part, L, adaptive, variant, c->stream);
     } else {
         rc = launch_force_fp64(pos, part, L, adaptive, c->avg_mass, c->stream);
@@ -190,11 +190,12 @@ int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const 
 // part[0..S) = partial sums of F(x) for the owned i-slice; returns S. Multi-GPU: the own j-slice is processed while the
 // all-gather of the remote slices is in flight on comm_stream.
 int eval_force(nb_ctx* c, int* S_out) {
-    const int R = c->precision == NB_PREC_FP32 ? 2 : 2;
+    const int R = c->precision == NB_PREC_FP32 ? force_i_tiles_per_cta(c->force_variant == 0 ? 3 : c->force_variant) : 2;
     const int nit = (int)(c->ni / kTJ), it0 = (int)(c->i0 / kTJ);
     const int iblocks = nit / R;
     ForceLaunch L; L.it0 = it0; L.nit = nit; L.ntiles = c->ntiles; L.npad = c->npad;
     L.kappa = c->kappa > 0.f ? c->kappa : 3.0e38f;
+    L.g0 = c->avg_mass > 0.0 ? (float)(kG * c->avg_mass) : 1.f;
     const int slot = (int)(c->fev_count % nb_ctx::kRing);
     NB_CUDA(cudaEventRecord(c->fev0[slot], c->stream));
     if (c->world == 1) {
@@ -343,7 +344,7 @@ int nb_set_methods(nb_ctx* c, int integ, int force, int subtract_com) {
 
 int nb_set_option(nb_ctx* c, const char* key, long value) {
     if (!c || !key) return fail(NB_ERR_INVALID, "nb_set_option: NULL argument");
-    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 2) return fail(NB_ERR_INVALID, "force_variant must be 0..2"); c->force_variant = (int)value; return NB_OK; }
+    if (!strcmp(key, "force_variant")) { if (value < 0 || value > 3) return fail(NB_ERR_INVALID, "force_variant must be 0..3"); c->force_variant = (int)value; return NB_OK; }
     if (!strcmp(key, "j_splits")) { if (value < 0 || value > 64) return fail(NB_ERR_INVALID, "j_splits must be 0..64"); c->j_splits = (int)value; return NB_OK; }
     if (!strcmp(key, "spatial_sort")) { c->spatial_sort = value ? 1 : 0; return NB_OK; }
     if (!strcmp(key, "far_kappa_milli")) { if (value < 0) return fail(NB_ERR_INVALID, "far_kappa_milli must be >= 0"); c->kappa = (float)value * 1e-3f; return NB_OK; }

@@ -50,6 +50,29 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  :: "r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
+// ---- FP64 building blocks (FP64 kernel and the FP64 near-field path of the FP32 production kernel) --------------------
+__device__ __forceinline__ double rsq64_seed(double x) { double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y; }
+
+// gm * s2^(-3/2) to full double precision without the branches of the library rsqrt(): seed y0 from MUFU.RSQ64H
+// (~1e-6), e = 1 - s2 y0^2, then s2^(-3/2) = y0^3 (1 + 3/2 e + 15/8 e^2 + O(e^3)). 7 DP operations.
+__device__ __forceinline__ double gm_inv_r3(double s2, double gm) {
+    const double y0 = rsq64_seed(s2);
+    const double t = y0 * y0;
+    const double e = fma(s2, -t, 1.0);
+    const double sc0 = (gm * y0) * t;
+    const double c = e * fma(e, 1.875, 1.5);
+    return fma(sc0, c, sc0);
+}
+// q^(2/3) for q >= 0: y0 ~ q^(-1/3) from the FP32 MUFU (lg2/ex2), one Newton step for y = q^(-1/3) in double
+// (y1 = y0 (4 - q y0^3) / 3, error ~2e-12 relative), q^(2/3) = q y1. Replaces cbrt() of core/Forces.cpp:354.
+__device__ __forceinline__ double pow23(double q) {
+    const float qf = fmaxf((float)q, 1e-30f);
+    const double y0 = (double)ex2_approx(lg2_approx(qf) * -0.3333333333333333f);
+    const double a = q * y0;
+    const double b = a * (y0 * y0);
+    return a * fma(b, -0.3333333333333333, 1.3333333333333333);
+}
+
 // ------------------------------------------------------------------------------------------------------------------
 // Register-resident i-particles: R per thread, every value duplicated into both halves of a register pair so that one
 // packed instruction handles two j-particles.
@@ -147,9 +170,10 @@ __device__ __forceinline__ void tile_pass(IState<R, ADAPTIVE>& S, const float* _
             interact4<R, ADAPTIVE, FAR>(S, hi, lo, gmrow, mqrow, j4);
 #pragma unroll
         for (int r = 0; r < R; ++r) {      // flush 128 j's of FP32 partial sums into the FP64 accumulators
-            S.dax[r] += (double)(S.ax[r].x + S.ax[r].y); S.ax[r] = make_float2(0.f, 0.f);
-            S.day[r] += (double)(S.ay[r].x + S.ay[r].y); S.ay[r] = make_float2(0.f, 0.f);
-            S.daz[r] += (double)(S.az[r].x + S.az[r].y); S.az[r] = make_float2(0.f, 0.f);
+            S.dax[r] += (double)(S.ax[r].x + S.ax[r].y);
+            S.day[r] += (double)(S.ay[r].x + S.ay[r].y);
+            S.daz[r] += (double)(S.az[r].x + S.az[r].y);
+            S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
         }
     }
 }
@@ -360,30 +384,255 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
 }
 
 // ------------------------------------------------------------------------------------------------------------------
+// Variant 3 (production): FP32 far field with FOUR i-particles per thread + FP64 near field.
+//
+// Measured on B200 (tools/pipe_bench, profiles/): a broadcast LDS.128 costs the issuing sub-partition ~4.6 cycles of
+// FMA-pipe time, so with two i-particles per thread (variant 2) the four loads of a j4 group add ~20 % to the 88 pipe
+// cycles of its 8 interactions. Four i-particles per thread halve that. To make room in the register file
+//   * only the far-path state of the i-particles (one float per coordinate, CTA frame) lives in registers,
+//   * the FP64 running sums live in shared memory (touched once per 128 j),
+//   * the near field (the few adjacent tiles) is evaluated one i-tile at a time in FP64, re-deriving the i-particle from
+//     the packed tile. FP64 there is also what keeps the result accurate when two close neighbours pull in opposite
+//     directions (pair terms 100x larger than their sum): those terms are now exact to ~1e-15 instead of ~1e-7.
+// Per j-tile the four i-tiles of the CTA are classified independently (bit r of `mask` = i-tile r is far).
+constexpr int kR4 = 4;
+constexpr int kFarFloats = 4 * kTJ;                         // rows k x', k y', k z', k  (PAIRWISE)  |  x', y', z', -  (ADAPTIVE)
+constexpr int kXfFloats = kFarFloats + 3 * kTJ * 2;         // + three rows of doubles (x', y', z') for the FP64 near path
+constexpr size_t kR4SmemBytes = (size_t)kStages * kTileBytes + 2 * (size_t)kXfFloats * 4 + (size_t)kR4 * 3 * kTJ * 8 + 32 + kStages * 8;
+
+template <bool ADAPTIVE>
+struct IState4 {
+    float2 nx[kR4], ny[kR4], nz[kR4];   // -(x'_i) duplicated in both halves (CTA frame)
+    float2 mq[kR4];                     // m_i / (3 mean mass) (ADAPTIVE)
+    float2 ax[kR4], ay[kR4], az[kR4];   // FP32 partial sums
+};
+
+// far field: the four i-particles of the thread against one j4 group.
+//   PAIRWISE: mass-scaled frame — the tile holds k_j x'_j and k_j with k_j = sqrt(G0 / (G m_j)); d' = k_j (x'_j - x'_i) is
+//   one FFMA2 per coordinate and (G m_j / G0) d / r^3 = d' / |d'|^3, so the multiplication by G m_j disappears
+//   (11 packed operations per pair; measured 3 % faster than the 12-operation form in this kernel).
+//   ADAPTIVE: plain frame, G m_j and m_j/(3 mbar) from the raw tile.
+//   MASKED: i-tiles whose bit in `mask` is clear are in the near field of this j-tile and are handled in FP64
+//   elsewhere; their contribution is switched off here (the select also removes the inf of a self pair).
+template <bool ADAPTIVE, bool MASKED>
+__device__ __forceinline__ void far_j4(IState4<ADAPTIVE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
+                                       int j4, uint32_t mask) {
+    const float4 X = reinterpret_cast<const float4*>(Tf + 0 * kTJ)[j4];
+    const float4 Y = reinterpret_cast<const float4*>(Tf + 1 * kTJ)[j4];
+    const float4 Z = reinterpret_cast<const float4*>(Tf + 2 * kTJ)[j4];
+    const float4 K = ADAPTIVE ? reinterpret_cast<const float4*>(raw + 3 * kTJ)[j4]       // G m_j
+                              : reinterpret_cast<const float4*>(Tf + 3 * kTJ)[j4];       // k_j
+    float4 MQ = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ADAPTIVE) MQ = reinterpret_cast<const float4*>(raw + 7 * kTJ)[j4];
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const float2 xj = p ? make_float2(X.z, X.w) : make_float2(X.x, X.y);
+        const float2 yj = p ? make_float2(Y.z, Y.w) : make_float2(Y.x, Y.y);
+        const float2 zj = p ? make_float2(Z.z, Z.w) : make_float2(Z.x, Z.y);
+        const float2 kj = p ? make_float2(K.z, K.w) : make_float2(K.x, K.y);
+        const float2 mqj = p ? make_float2(MQ.z, MQ.w) : make_float2(MQ.x, MQ.y);
+#pragma unroll
+        for (int r = 0; r < kR4; ++r) {
+            float2 dx, dy, dz;
+            if (!ADAPTIVE) {
+                dx = __ffma2_rn(S.nx[r], kj, xj); dy = __ffma2_rn(S.ny[r], kj, yj); dz = __ffma2_rn(S.nz[r], kj, zj);
+            } else {
+                dx = __fadd2_rn(xj, S.nx[r]); dy = __fadd2_rn(yj, S.ny[r]); dz = __fadd2_rn(zj, S.nz[r]);
+            }
+            float2 r2 = __fmul2_rn(dz, dz);
+            r2 = __ffma2_rn(dy, dy, r2);
+            r2 = __ffma2_rn(dx, dx, r2);
+            float2 s2 = r2;
+            if (ADAPTIVE) {
+                const float2 q = __fadd2_rn(mqj, S.mq[r]);
+                float2 lg; lg.x = lg2_approx(q.x); lg.y = lg2_approx(q.y);
+                const float kLog2Eta2 = -13.287712379549449f;
+                const float2 e = __ffma2_rn(lg, make_float2(0.6666666666666666f, 0.6666666666666666f), make_float2(kLog2Eta2, kLog2Eta2));
+                float2 w; w.x = ex2_approx(e.x); w.y = ex2_approx(e.y);
+                const float2 sa = __ffma2_rn(r2, w, r2);
+                const float2 sb = __fadd2_rn(r2, make_float2(1e-8f, 1e-8f));
+                s2.x = fmaxf(sa.x, sb.x); s2.y = fmaxf(sa.y, sb.y);
+            }
+            float2 ri; ri.x = rsq_approx(s2.x); ri.y = rsq_approx(s2.y);
+            if (MASKED) {
+                const bool on = (mask >> r) & 1u;
+                ri.x = on ? ri.x : 0.f; ri.y = on ? ri.y : 0.f;
+            }
+            const float2 ri2 = __fmul2_rn(ri, ri);
+            float2 sc;
+            if (!ADAPTIVE) sc = __fmul2_rn(ri, ri2);
+            else { sc = __fmul2_rn(kj, ri); sc = __fmul2_rn(sc, ri2); }
+            S.ax[r] = __ffma2_rn(sc, dx, S.ax[r]); S.ay[r] = __ffma2_rn(sc, dy, S.ay[r]); S.az[r] = __ffma2_rn(sc, dz, S.az[r]);
+        }
+    }
+}
+
+// whole tile, far field; FP32 partial sums are flushed into the FP64 sums in shared memory (thread-private slots)
+// every 128 j. PAIRWISE sums are in units of G0 (mass-scaled frame).
+template <bool ADAPTIVE, bool MASKED>
+__device__ __forceinline__ void far_tile(IState4<ADAPTIVE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
+                                         double* __restrict__ dacc, int t, float g0, uint32_t mask) {
+    const float unit = ADAPTIVE ? 1.f : g0;
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+#pragma unroll 2
+        for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4) far_j4<ADAPTIVE, MASKED>(S, Tf, raw, j4, mask);
+#pragma unroll
+        for (int r = 0; r < kR4; ++r) {
+            double* d = dacc + (size_t)r * 3 * kTJ + t;
+            d[0] += (double)((S.ax[r].x + S.ax[r].y) * unit);
+            d[kTJ] += (double)((S.ay[r].x + S.ay[r].y) * unit);
+            d[2 * kTJ] += (double)((S.az[r].x + S.az[r].y) * unit);
+            S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
+        }
+    }
+}
+
+// whole tile, FP64 near field, ONE i-particle (i-tile `itile`, lane t), CTA frame origin O
+template <bool ADAPTIVE>
+__device__ __forceinline__ void near_tile64(const float* __restrict__ pk, int itile, int t, const float* __restrict__ O,
+                                            const double* __restrict__ Td, const float* __restrict__ raw,
+                                            double* __restrict__ d3 /* dacc + r*3*kTJ + t */) {
+    const float* p = pk + (size_t)itile * kTileFloats + t;
+    const double xi = ((double)p[0 * kTJ] - (double)O[0]) + (double)p[4 * kTJ];
+    const double yi = ((double)p[1 * kTJ] - (double)O[1]) + (double)p[5 * kTJ];
+    const double zi = ((double)p[2 * kTJ] - (double)O[2]) + (double)p[6 * kTJ];
+    const double mqi = ADAPTIVE ? (double)p[7 * kTJ] : 0.0;
+    double ax = 0.0, ay = 0.0, az = 0.0;
+#pragma unroll 4
+    for (int j = 0; j < kTJ; ++j) {
+        const double dx = Td[j] - xi, dy = Td[kTJ + j] - yi, dz = Td[2 * kTJ + j] - zi;
+        const double gm = (double)raw[3 * kTJ + j] + (double)raw[kGmLoRow * kTJ + j];
+        const double r2 = dx * dx + dy * dy + dz * dz;
+        double s2 = r2;
+        if (ADAPTIVE) {
+            const double w = pow23(mqi + (double)raw[7 * kTJ + j]);
+            s2 = fmax(fma(r2 * w, 1e-4, r2), r2 + 1e-8);
+        }
+        double sc = gm_inv_r3(s2, gm);
+        sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;      // cut-off and self pair
+        ax = fma(sc, dx, ax); ay = fma(sc, dy, ay); az = fma(sc, dz, az);
+    }
+    d3[0] += ax; d3[kTJ] += ay; d3[2 * kTJ] += az;
+}
+
+// per-i-tile bounding boxes of the CTA: thread r (< kR4) owns box r and classifies the j-tiles for it
+struct IBox1 { float lo[3], hi[3]; };
+
+template <bool ADAPTIVE>
+__global__ void __launch_bounds__(kThreads, 2)
+force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* raw = reinterpret_cast<float*>(smem_raw);                                        // [kStages][kTileFloats]
+    float* T = raw + kStages * kTileFloats;                                                 // [2][kXfFloats]
+    double* dacc = reinterpret_cast<double*>(T + 2 * kXfFloats);                            // [kR4*3][kTJ]
+    uint32_t* flags = reinterpret_cast<uint32_t*>(dacc + kR4 * 3 * kTJ);                    // [2][4] far flag of i-tile r, by tile parity
+    uint64_t* full = reinterpret_cast<uint64_t*>(flags + 8);                                // [kStages]
+    const int t = threadIdx.x, s = blockIdx.y;
+    const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
+    const int cnt = k1 - k0;
+    const int itile_first = L.it0 + blockIdx.x * kR4;
+    if (t == 0) {
+#pragma unroll
+        for (int b = 0; b < kStages; ++b) mbar_init(&full[b], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+#pragma unroll
+    for (int k = 0; k < kR4 * 3; ++k) dacc[k * kTJ + t] = 0.0;
+    __syncthreads();
+    if (t == 0) {
+        const int pre = cnt < kStages ? cnt : kStages;
+        for (int q = 0; q < pre; ++q) {
+            mbar_expect_tx(&full[q], kTileBytes);
+            bulk_g2s(raw + q * kTileFloats, pk + (size_t)wrap_tile(L.jt0 + k0 + q, L.ntiles) * kTileFloats, kTileBytes, &full[q]);
+        }
+    }
+    CtaFrame F;
+    load_frame<kR4>(F, pk, itile_first);
+    IBox1 B;                                   // box of i-tile min(t, 3); only threads 0..3 use it
+    {
+        const float* m = pk + (size_t)(itile_first + (t < kR4 ? t : kR4 - 1)) * kTileFloats + kMetaRow * kTJ;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { B.lo[c] = __ldg(m + c); B.hi[c] = __ldg(m + 3 + c); }
+    }
+    const float inv_g0 = 1.f / L.g0;
+    IState4<ADAPTIVE> S;
+#pragma unroll
+    for (int r = 0; r < kR4; ++r) {
+        const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
+        float v;
+        v = -((p[0 * kTJ] - F.O[0]) + p[4 * kTJ]); S.nx[r] = make_float2(v, v);
+        v = -((p[1 * kTJ] - F.O[1]) + p[5 * kTJ]); S.ny[r] = make_float2(v, v);
+        v = -((p[2 * kTJ] - F.O[2]) + p[6 * kTJ]); S.nz[r] = make_float2(v, v);
+        v = ADAPTIVE ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
+        S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
+    }
+    // classify (thread r < 4) and re-express (thread t <-> particle t) tile q into buffer q & 1
+    auto prepare = [&](int q) {
+        const float* rw = raw + (q % kStages) * kTileFloats;
+        float* Tf = T + (q & 1) * kXfFloats;
+        double* Td = reinterpret_cast<double*>(Tf + kFarFloats);
+        const float* meta = rw + kMetaRow * kTJ;
+        if (t < kR4) {
+            float g2 = 0.f, hj = 0.f;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                const float g = fmaxf(0.f, fmaxf(meta[c] - B.hi[c], B.lo[c] - meta[3 + c]));
+                g2 = fmaf(g, g, g2);
+                hj = fmaxf(hj, 0.5f * (meta[3 + c] - meta[c]));
+            }
+            const float thr = L.kappa * (F.half + hj);          // F.half: half-extent of the whole i-block (frame size)
+            flags[(q & 1) * 4 + t] = ((g2 > thr * thr) && (g2 > 1e-8f)) ? 1u : 0u;
+        }
+        float kj = 1.f;     // PAIRWISE: k_j = sqrt(G0 / (G m_j)); massless particles get a huge finite k, their r'^2 overflows
+                            // to +inf, rsqrt gives 0 and they contribute exactly nothing
+        if (!ADAPTIVE) { kj = rsq_approx(fmaxf(rw[3 * kTJ + t] * inv_g0, 1e-30f)); Tf[3 * kTJ + t] = kj; }
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float xh = rw[c * kTJ + t], xl = rw[(4 + c) * kTJ + t];
+            Tf[c * kTJ + t] = ((xh - F.O[c]) + xl) * kj;
+            Td[c * kTJ + t] = ((double)xh - (double)F.O[c]) + (double)xl;
+        }
+    };
+    if (cnt > 0) { mbar_wait(&full[0], 0u); prepare(0); }
+    __syncthreads();
+    for (int q = 0; q < cnt; ++q) {
+        const int b = q % kStages;
+        if (q + 1 < cnt) {                     // classify + re-express the next tile while this one is being computed
+            mbar_wait(&full[(q + 1) % kStages], (uint32_t)(((q + 1) / kStages) & 1));
+            prepare(q + 1);
+        }
+        const uint4 fl = *reinterpret_cast<const uint4*>(flags + (q & 1) * 4);
+        const uint32_t mask = fl.x | (fl.y << 1) | (fl.z << 2) | (fl.w << 3);
+        const float* rw = raw + b * kTileFloats;
+        const float* Tf = T + (q & 1) * kXfFloats;
+        const double* Td = reinterpret_cast<const double*>(Tf + kFarFloats);
+        if (mask == 0xFu) {
+            far_tile<ADAPTIVE, false>(S, Tf, rw, dacc, t, L.g0, mask);
+        } else {
+            if (mask != 0u) far_tile<ADAPTIVE, true>(S, Tf, rw, dacc, t, L.g0, mask);
+#pragma unroll 1
+            for (int r = 0; r < kR4; ++r)
+                if (!((mask >> r) & 1u)) near_tile64<ADAPTIVE>(pk, itile_first + r, t, F.O, Td, rw, dacc + (size_t)r * 3 * kTJ + t);
+        }
+        __syncthreads();                       // all warps done with raw[b], T[q&1], flags[q&1]; tile q+1 is prepared
+        if (t == 0 && q + kStages < cnt) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_expect_tx(&full[b], kTileBytes);
+            bulk_g2s(raw + b * kTileFloats, pk + (size_t)wrap_tile(L.jt0 + k0 + q + kStages, L.ntiles) * kTileFloats, kTileBytes, &full[b]);
+        }
+    }
+    double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad;
+#pragma unroll
+    for (int r = 0; r < kR4; ++r) {
+        const size_t i = (size_t)(itile_first + r) * kTJ + t;
+        o[i] = dacc[(r * 3 + 0) * kTJ + t]; o[(size_t)L.npad + i] = dacc[(r * 3 + 1) * kTJ + t]; o[2 * (size_t)L.npad + i] = dacc[(r * 3 + 2) * kTJ + t];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
 // FP64 mode. Tiles of 256 double4 (x,y,z,m) straight from the master array; R = 2 i-particles per thread.
 constexpr int kR64 = 2;
-
-__device__ __forceinline__ double rsq64_seed(double x) { double y; asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x)); return y; }
-
-// gm * s2^(-3/2) to full double precision without the branches of the library rsqrt(): seed y0 from MUFU.RSQ64H
-// (~1e-6), e = 1 - s2 y0^2, then s2^(-3/2) = y0^3 (1 + 3/2 e + 15/8 e^2 + O(e^3)). 7 DP operations.
-__device__ __forceinline__ double gm_inv_r3(double s2, double gm) {
-    const double y0 = rsq64_seed(s2);
-    const double t = y0 * y0;
-    const double e = fma(s2, -t, 1.0);
-    const double sc0 = (gm * y0) * t;
-    const double c = e * fma(e, 1.875, 1.5);
-    return fma(sc0, c, sc0);
-}
-// q^(2/3) for q >= 0: y0 ~ q^(-1/3) from the FP32 MUFU (lg2/ex2), one Newton step for y = q^(-1/3) in double
-// (y1 = y0 (4 - q y0^3) / 3, error ~2e-12 relative), q^(2/3) = q y1. Replaces cbrt() of core/Forces.cpp:354.
-__device__ __forceinline__ double pow23(double q) {
-    const float qf = fmaxf((float)q, 1e-30f);
-    const double y0 = (double)ex2_approx(lg2_approx(qf) * -0.3333333333333333f);
-    const double a = q * y0;
-    const double b = a * (y0 * y0);
-    return a * fma(b, -0.3333333333333333, 1.3333333333333333);
-}
 
 template <bool ADAPTIVE>
 __global__ void __launch_bounds__(kThreads, 2)
@@ -485,10 +734,27 @@ int regs_of(K kernel) {
 
 } // namespace
 
-constexpr int kR32 = 2;   // i-particles per thread in FP32 mode
+constexpr int kR32 = 2;   // i-particles per thread of variants 1 and 2
+
+int force_i_tiles_per_cta(int variant) { return variant == 3 ? kR4 : kR32; }
 
 int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, bool adaptive, int variant, cudaStream_t st) {
     if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
+    if (variant == 3) {
+        if (L.nit % kR4 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR4);
+        static bool attr_set[64] = {};
+        int dev = 0; NB_CUDA(cudaGetDevice(&dev));
+        if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+            NB_CUDA(cudaFuncSetAttribute(force_fp32_r4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kR4SmemBytes));
+            NB_CUDA(cudaFuncSetAttribute(force_fp32_r4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kR4SmemBytes));
+            attr_set[dev] = true;
+        }
+        dim3 grid(L.nit / kR4, L.S), block(kThreads);
+        if (adaptive) force_fp32_r4_kernel<true><<<grid, block, kR4SmemBytes, st>>>(pk, part, L);
+        else          force_fp32_r4_kernel<false><<<grid, block, kR4SmemBytes, st>>>(pk, part, L);
+        NB_CUDA(cudaGetLastError());
+        return NB_OK;
+    }
     if (L.nit % kR32 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR32);
     dim3 grid(L.nit / kR32, L.S), block(kThreads);
     if (variant == 2) {
@@ -521,7 +787,8 @@ int launch_potential_fp64(const double4* pos, double* pot, long npad, int ntiles
 }
 
 int force_regs_info(char* buf, int len) {
-    return snprintf(buf, len, "fp32_ld:%d fp32_ld_adaptive:%d fp32_tma:%d fp32_tma_adaptive:%d fp64:%d fp64_adaptive:%d",
+    return snprintf(buf, len, "fp32_r4:%d fp32_r4_adaptive:%d fp32_ld:%d fp32_ld_adaptive:%d fp32_tma:%d fp32_tma_adaptive:%d fp64:%d fp64_adaptive:%d",
+                    regs_of(force_fp32_r4_kernel<false>), regs_of(force_fp32_r4_kernel<true>),
                     regs_of(force_fp32_ld_kernel<kR32, false>), regs_of(force_fp32_ld_kernel<kR32, true>),
                     regs_of(force_fp32_tma_kernel<kR32, false>), regs_of(force_fp32_tma_kernel<kR32, true>),
                     regs_of(force_fp64_kernel<false>), regs_of(force_fp64_kernel<true>));

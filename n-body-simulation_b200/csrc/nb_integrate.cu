@@ -38,7 +38,10 @@ __device__ __forceinline__ void pack_one(float* __restrict__ pk, long i, const d
     float* o = pk + (size_t)(i / kTJ) * kTileFloats + (i % kTJ);
     const float xh = (float)p.x, yh = (float)p.y, zh = (float)p.z;
     o[0 * kTJ] = xh; o[1 * kTJ] = yh; o[2 * kTJ] = zh;
-    o[3 * kTJ] = (float)(kG * p.w);
+    const double gmd = kG * p.w;
+    const float gmh = (float)gmd;
+    o[3 * kTJ] = gmh;
+    o[kGmLoRow * kTJ] = (float)(gmd - (double)gmh);
     o[4 * kTJ] = (float)(p.x - (double)xh);
     o[5 * kTJ] = (float)(p.y - (double)yh);
     o[6 * kTJ] = (float)(p.z - (double)zh);

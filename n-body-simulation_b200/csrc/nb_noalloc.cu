@@ -11,7 +11,7 @@
 // For them this file offers ONE call that takes caller-owned device arrays in and out and keeps all of its intermediate
 // data — the packed FP32 tiles and the per-split partial sums that the force kernel normally gets from the context — in a
 // fixed block of device memory that is part of the library image itself (g_noalloc_scratch below). The price is a hard
-// size limit (NB_NOALLOC_MAX_N particles) and ~7.5 MB of every GPU's memory that loads the library, held until exit.
+// size limit (NB_NOALLOC_MAX_N particles) and ~7.6 MB of every GPU's memory that loads the library, held until exit.
 //
 // What to know before using it:
 //   * The first call on each device looks up the device address of the block (cudaGetSymbolAddress) and remembers it;
@@ -26,8 +26,8 @@
 
 #include <mutex>
 
-// Capacity: NB_NOALLOC_MAX_N particles (32768) -> 1,179,648 bytes of packed tiles + 8 partial-sum slots of
-// 3 x 32768 doubles (6,291,456 bytes) = 7,471,104 bytes per GPU.
+// Capacity: NB_NOALLOC_MAX_N particles (32768) -> 1,310,720 bytes of packed tiles + 8 partial-sum slots of
+// 3 x 32768 doubles (6,291,456 bytes) = 7,602,176 bytes per GPU.
 constexpr long   kNoallocMaxN   = NB_NOALLOC_MAX_N;                 // multiple of nb::kAlign
 constexpr int    kNoallocSplits = 8;                                // upper bound of j-splits (partial-sum slots)
 constexpr size_t kTilesBytes    = (size_t)kNoallocMaxN * nb::kNC * sizeof(float);
@@ -46,7 +46,7 @@ constexpr int kMaxDevices = 64;
 std::mutex g_setup_mutex;
 unsigned char* g_scratch_addr[kMaxDevices] = {};       // per device: device address of g_noalloc_scratch on that device
 
-// caller-order double4 positions -> packed tiles (rows 0..7; the meta row is not read by the variant-1 kernel)
+// caller-order double4 positions -> packed tiles (rows 0..7 and 9; the meta row 8 is not read by the variant-1 kernel)
 __global__ void __launch_bounds__(kThreads)
 noalloc_pack_kernel(const double4* __restrict__ pos, long n, float* __restrict__ pk, double inv3mbar) {
     const long i = (long)blockIdx.x * kThreads + threadIdx.x;        // grid covers exactly npad particles
@@ -55,7 +55,10 @@ noalloc_pack_kernel(const double4* __restrict__ pos, long n, float* __restrict__
     float* o = pk + (size_t)(i / kTJ) * kTileFloats + (i % kTJ);
     const float xh = (float)p.x, yh = (float)p.y, zh = (float)p.z;
     o[0 * kTJ] = xh; o[1 * kTJ] = yh; o[2 * kTJ] = zh;
-    o[3 * kTJ] = (float)(kG * p.w);
+    const double gmd = kG * p.w;
+    const float gmh = (float)gmd;
+    o[3 * kTJ] = gmh;
+    o[kGmLoRow * kTJ] = (float)(gmd - (double)gmh);
     o[4 * kTJ] = (float)(p.x - (double)xh);
     o[5 * kTJ] = (float)(p.y - (double)yh);
     o[6 * kTJ] = (float)(p.z - (double)zh);
@@ -132,7 +135,7 @@ extern "C" int nb_force_noalloc(int force_method, const double* d_posMass4, doub
     NB_CUDA(cudaGetLastError());
 
     ForceLaunch L;
-    L.it0 = 0; L.nit = ntiles; L.jt0 = 0; L.jcount = ntiles; L.ntiles = ntiles; L.npad = npad; L.s0 = 0; L.S = S; L.kappa = 3.0e38f;
+    L.it0 = 0; L.nit = ntiles; L.jt0 = 0; L.jcount = ntiles; L.ntiles = ntiles; L.npad = npad; L.s0 = 0; L.S = S; L.kappa = 3.0e38f; L.g0 = 1.f;
     rc = launch_force_fp32(pk, part, L, adaptive, /*variant=*/1, st); if (rc) return rc;
 
     noalloc_reduce_kernel<<<(unsigned)((n + kThreads - 1) / kThreads), kThreads, 0, st>>>(part, S, npad, n, reinterpret_cast<double4*>(d_accel4));
