@@ -27,6 +27,33 @@ def gpu_accel(lib, pm, v, force, prec, **opts):
         return ctx.accel()
 
 
+def _tracers():
+    """Massless tracer particles inside a massive system (m = 0 must neither attract nor be skipped as a target)."""
+    pm, v = nbtest.gen_spiral(3000, seed=8)
+    pm[::7, 3] = 0.0
+    return pm, v
+
+
+def _coincident():
+    """Every particle at the same point: all pairs are below the cut-off, accelerations are exactly zero."""
+    pm = np.zeros((700, 4)); pm[:, :3] = [1.5, -2.0, 0.25]; pm[:, 3] = 1.0
+    return pm, np.zeros((700, 4))
+
+
+def _offset():
+    """A system far from the origin (|x| ~ 4e7 AU, separations ~ 10 AU): exercises the two-float positions."""
+    pm, v = nbtest.gen_spiral(6000, seed=9)
+    pm[:, :3] += [1.0e7, -2.0e7, 3.0e7]
+    return pm, v
+
+
+def _mass_range():
+    """18 decades of mass in one system (mass-scaled far path: k_j = sqrt(G0 / G m_j))."""
+    pm, v = nbtest.gen_random(5000, seed=10)
+    pm[:, 3] = 10.0 ** np.random.default_rng(10).uniform(-12, 6, 5000)
+    return pm, v
+
+
 DATASETS = {
     "three_body": lambda: (GOLD["kat1_pm"].copy(), np.zeros((3, 4))),
     "sistema": lambda: (GOLD["sis_pm"].copy(), GOLD["sis_v"].copy()),
@@ -37,6 +64,10 @@ DATASETS = {
     "random_5000_ragged": lambda: nbtest.gen_random(5000, seed=43),
     "spiral_16384": lambda: nbtest.gen_spiral(16384, seed=42),
     "galaxy_planets_3001": lambda: nbtest.gen_galaxy(1000, 2, seed=42),
+    "massless_tracers": _tracers,
+    "coincident": _coincident,
+    "far_from_origin": _offset,
+    "mass_range_1e18": _mass_range,
 }
 
 
