@@ -9,8 +9,8 @@ NVFLAGS:= $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Iinclude -I$(CSRC) 
 CU_SRCS := $(CSRC)/nb_force.cu $(CSRC)/nb_integrate.cu $(CSRC)/nb_sort.cu $(CSRC)/nb_context.cu $(CSRC)/nb_noalloc.cu
 CU_OBJS := $(CU_SRCS:.cu=.o)
 
-.PHONY: all lib oracle ref refgpu tools host clean
-all: lib oracle ref tools host refgpu
+.PHONY: all lib oracle ref refgpu refcuda tools host clean
+all: lib oracle ref tools host refgpu refcuda
 
 lib: $(LIB)
 $(CSRC)/%.o: $(CSRC)/%.cu $(CSRC)/nb_common.cuh include/nbody_b200.h
@@ -24,6 +24,8 @@ ref:
 	$(MAKE) -C oracle ref
 refgpu: lib
 	$(MAKE) -C oracle refgpu
+refcuda:
+	$(MAKE) -C oracle refcuda
 
 tools: tools/pipe_bench
 tools/pipe_bench: tools/pipe_bench.cu

@@ -101,6 +101,22 @@ def ncu_traffic_bytes(n, force, prec, world):
         return None
 
 
+def reference_cuda_bar(n):
+    """Second same-box bar: the reference's own FP64 CUDA kernels compiled unmodified for sm_100a
+    (oracle/_ref/ref_cuda_bench, built in the container where /root/reference exists), driven through the reference's
+    runBenchmarkOnGPU on a spiral galaxy of the workload's size (2 steps + initial force). None if the binary is absent."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_cuda_bench")
+    if not os.path.exists(exe):
+        return None
+    try:
+        r = subprocess.run([exe, str(n), "2", "0", "256"], capture_output=True, text=True, timeout=300)
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+        return {"value": d["Gint_per_s"], "unit": "Gint/s", "seconds": d["seconds"], "impl": d["impl"],
+                "note": "runBenchmarkOnGPU(BLOCK_SIZE=256) incl. its per-call cudaMalloc/H2D/D2H, FP64, no COM removal"}
+    except Exception as e:  # noqa: BLE001  (a baseline that cannot run must not fail the bench)
+        return {"unavailable": str(e)[:200]}
+
+
 def pinned(n_rows):
     import torch
     t = torch.empty((n_rows, 4), dtype=torch.float64).pin_memory()
@@ -293,7 +309,9 @@ def main():
         per_gpu_interactions = interactions / world
         ach_int = per_gpu_interactions / (fk_ms * 1e-3)
         peak_int = n_sm * (128.0 / SLOTS_PER_INTERACTION) * f_max
-        roofline = {"bound": "fp32-issue (not hbm, not tensor: 13 FP32-pipe slots + 1 MUFU per interaction, SURVEY.md 8d)",
+        roofline = {"bound": "fp32",
+                    "bound_note": "compute-bound on FP32 issue (not hbm, not tensor): 13 FP32-pipe slots + 1 MUFU per PAIRWISE "
+                                  "interaction (SURVEY.md 8d); achieved/peak are interactions/s x 13 slots x 2 flop",
                     "achieved": ach_int * SLOTS_PER_INTERACTION * 2 / 1e12,
                     "peak": peak_int * SLOTS_PER_INTERACTION * 2 / 1e12, "unit": "TFLOP/s",
                     "frac": ach_int / peak_int, "traffic": ncu_traffic_bytes(n, force, prec, world),
@@ -320,6 +338,11 @@ def main():
         if not args.no_cpu_baseline and world >= 1:
             cb, _ = cpu_baseline(n)
             line["cpu_baseline"] = cb
+            if world == 1:
+                ctx.close()                      # free the device before the reference's kernels allocate
+                rc = reference_cuda_bar(n)
+                if rc:
+                    line["reference_cuda_fp64"] = rc
         print(json.dumps(line), flush=True)
     ctx.close()
     if world > 1:

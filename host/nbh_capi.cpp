@@ -32,6 +32,10 @@ int nbh_init_random(int n, double minMass, double maxMass, double L, double maxV
                     long cap, long* n_out, double* posMass4, double* vel4) {
     return guard([&] { return fill(nbh::init_random(n, minMass, maxMass, L, maxVel, minDist, &seed), cap, n_out, posMass4, vel4, nullptr, 0); });
 }
+int nbh_save_snapshot(const char* path, long n, const double* posMass4, const double* vel4) {
+    return guard([&] { nbh::ParticleSet p((size_t)n); std::memcpy(p.posMass.data(), posMass4, (size_t)n * 32);
+                       std::memcpy(p.vel.data(), vel4, (size_t)n * 32); nbh::save_snapshot(path, p); return 0; });
+}
 // Parse + validate only: fills steps, stepFreq and the enum values. out[0..7] = steps, stepFreq, integ, force, exec, output, threads, hasSeed
 int nbh_parse_config(const char* config_text, long out[8]) {
     return guard([&] { nbh::Config c = nbh::parse_config_text(config_text);

@@ -53,6 +53,7 @@ Config parse_config_text(const std::string& text) {
     if (j.contains("precision")) c.precision = pick<int>(j["precision"].as_string(), {{"FP32", NB_PREC_FP32}, {"FP64", NB_PREC_FP64}}, "precision");
     if (j.contains("subtractCom")) c.subtractCom = j["subtractCom"].as_bool();
     if (j.contains("device")) c.device = j["device"].as_int();
+    if (j.contains("snapshotOut")) c.snapshotOut = j["snapshotOut"].as_string();
     return c;
 }
 
@@ -92,7 +93,37 @@ InitResult create_initial_conditions(const Config& cfg) {
 }
 
 // core/Initializer.cpp:17-53 — first token: body count; per body mass[kg] x y z[km] vx vy vz[km/s].
+void save_snapshot(const std::string& path, const ParticleSet& p) {
+    std::ofstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("Cannot open snapshot for writing: " + path);
+    const uint64_t n = p.n;
+    f.write("NBIN0001", 8);
+    f.write(reinterpret_cast<const char*>(&n), 8);
+    f.write(reinterpret_cast<const char*>(p.posMass.data()), (std::streamsize)(n * 32));
+    f.write(reinterpret_cast<const char*>(p.vel.data()), (std::streamsize)(n * 32));
+    if (!f) throw std::runtime_error("Short write to snapshot: " + path);
+}
+
+InitResult load_snapshot(const std::string& path, long count) {
+    std::ifstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("Cannot open file: " + path);
+    char magic[8]; uint64_t n = 0;
+    f.read(magic, 8); f.read(reinterpret_cast<char*>(&n), 8);
+    if (!f || std::string(magic, 8) != "NBIN0001") throw std::runtime_error("Not a NBIN0001 snapshot: " + path);
+    const uint64_t use = (count > 0 && (uint64_t)count < n) ? (uint64_t)count : n;
+    ParticleSet p((size_t)use);
+    f.read(reinterpret_cast<char*>(p.posMass.data()), (std::streamsize)(use * 32));
+    f.seekg((std::streamoff)(16 + n * 32));
+    f.read(reinterpret_cast<char*>(p.vel.data()), (std::streamsize)(use * 32));
+    if (!f) throw std::runtime_error("Truncated snapshot: " + path);
+    std::ostringstream md;
+    md << "# Initializer: binary snapshot\n# Total in file: " << n << "\n# Using first: " << use << "\n# Total particle count: "
+       << use << "\n# filePath: " << path << "\n";
+    return {std::move(p), md.str()};
+}
+
 InitResult init_from_file(const std::string& path, int count) {
+    if (path.size() > 5 && path.compare(path.size() - 5, 5, ".nbin") == 0) return load_snapshot(path, count);
     std::ifstream f(path);
     if (!f) throw std::runtime_error("Cannot open file: " + path);
     int total = 0; f >> total;
@@ -353,6 +384,7 @@ RunReport run_config(const Config& cfg, bool quiet) {
     }
     auto r1 = std::chrono::high_resolution_clock::now();
     rep.run_seconds = std::chrono::duration<double>(r1 - r0).count();
+    if (!cfg.snapshotOut.empty()) save_snapshot(cfg.snapshotOut, p);
     return rep;
 }
 

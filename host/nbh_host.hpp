@@ -6,6 +6,8 @@
 //     "precision": "FP32" | "FP64"   (default FP32 for BENCHMARK, FP64 for FILE_CSV)
 //     "subtractCom": true | false    (default true: the reference CPU integrators' behaviour)
 //     "device": integer
+//     "snapshotOut": "path.nbin"     — write the final state as a binary snapshot (checkpoint); a "FROM_FILE" filePath
+//                                      ending in ".nbin" reads one back (resume; partialCount <= 0 means all particles)
 #pragma once
 #include <cstddef>
 #include <string>
@@ -50,6 +52,7 @@ struct Config {
     int precision = -1;            // -1: choose by output mode
     bool subtractCom = true;
     int device = -1;
+    std::string snapshotOut;
 };
 
 Config parse_config_text(const std::string& text);
@@ -68,6 +71,11 @@ InitResult init_stellar_system(double starMass, int nPlanets, double planetMassM
                                const unsigned long* seed);
 InitResult init_spiral_galaxy(int nStars, double totalMass, int nArms, double galaxyRadius, double thickness,
                               double perturbation, const unsigned long* seed);
+
+// Binary snapshot (no counterpart in the reference, which can only read sistema.dat and never reads its own output):
+// "NBIN0001" | uint64 n | n x (x,y,z,m) doubles | n x (vx,vy,vz,0) doubles, little endian.
+void save_snapshot(const std::string& path, const ParticleSet& p);
+InitResult load_snapshot(const std::string& path, long count);
 
 // FILE_CSV sink (output/OutputUtils.cpp:8-59): metadata, header, one row per particle per snapshot.
 bool write_csv(const std::string& filename, const std::string& metadata, size_t n, size_t numTimeSteps,

@@ -115,6 +115,23 @@ def test_generators_are_seeded_and_shaped(host):
     assert "# Total in file: 25" in meta
 
 
+def test_binary_snapshot_roundtrip(host, tmp_path):
+    """Checkpoint/resume: a .nbin snapshot written by the host is read back bit-exactly through FROM_FILE."""
+    pm, v, _ = init_from(host, cfg_text(selected="GALAXY", seed=4))
+    path = str(tmp_path / "state.nbin")
+    host.nbh_save_snapshot.argtypes = [C.c_char_p, C.c_long, nbtest._dp, nbtest._dp]
+    assert host.nbh_save_snapshot(path.encode(), pm.shape[0], pm.ctypes.data_as(nbtest._dp), v.ctypes.data_as(nbtest._dp)) == 0
+    assert os.path.getsize(path) == 16 + pm.shape[0] * 64
+    text = cfg_text(selected="FROM_FILE").replace(json.dumps(os.path.join(nbtest.ROOT, "data_in", "sistema.dat")), json.dumps(path))
+    pm2, v2, meta = init_from(host, text.replace('"partialCount": 25', '"partialCount": 0'))
+    assert np.array_equal(pm, pm2) and np.array_equal(v, v2) and "binary snapshot" in meta
+    pm3, v3, _ = init_from(host, text.replace('"partialCount": 25', '"partialCount": 10'))
+    assert np.array_equal(pm[:10], pm3) and np.array_equal(v[:10], v3)
+    (tmp_path / "bad.nbin").write_bytes(b"garbage")
+    with pytest.raises(RuntimeError, match="NBIN0001"):
+        init_from(host, text.replace(json.dumps(path), json.dumps(str(tmp_path / "bad.nbin"))))
+
+
 def test_host_generators_match_reference_distributions(host, ref):
     pm, v, _ = init_from(host, cfg_text(selected="SPIRAL_GALAXY", seed=3))
     rp, rv = ref.init_spiral(5000)
