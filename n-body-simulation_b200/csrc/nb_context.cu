@@ -72,6 +72,7 @@ struct nb_ctx {
     long fev_count = 0;
     double4 *pos = nullptr, *vel = nullptr, *tmp4 = nullptr, *stage_pos = nullptr, *stage_vel = nullptr;
     unsigned int* perm = nullptr;          // perm[sorted slot] = caller index
+    double* snap = nullptr;                // snapshot staging [n][6] + [n][2], allocated by the first nb_snapshot
     SortScratch ss;
     int spatial_sort = 1; float kappa = 0.25f;
     double *acc = nullptr, *part = nullptr, *red_part = nullptr, *red = nullptr, *eout = nullptr;
@@ -88,11 +89,11 @@ namespace {
 
 void free_arrays(nb_ctx* c) {
     cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->tmp4); cudaFree(c->stage_pos); cudaFree(c->stage_vel);
-    cudaFree(c->acc); cudaFree(c->part); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->perm);
+    cudaFree(c->acc); cudaFree(c->part); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->perm); cudaFree(c->snap);
     cudaFree(c->ss.keys_in); cudaFree(c->ss.keys_out); cudaFree(c->ss.idx_in); cudaFree(c->ss.extent_part);
     cudaFree(c->ss.box); cudaFree(c->ss.cub_temp);
     c->pos = c->vel = c->tmp4 = c->stage_pos = c->stage_vel = nullptr;
-    c->acc = c->part = c->red_part = nullptr; c->pk = nullptr; c->perm = nullptr; c->part_bytes = 0;
+    c->acc = c->part = c->red_part = c->snap = nullptr; c->pk = nullptr; c->perm = nullptr; c->part_bytes = 0;
     c->ss = SortScratch();
     cudaGetLastError();
 }
@@ -521,18 +522,15 @@ int nb_snapshot(nb_ctx* c, double time, double* particleData6, double* systemDat
     double e[3];
     int rc = nb_energy(c, e); if (rc) return rc;
     systemData2[0] = time; systemData2[1] = e[0];
-    // stage through device scratch: [n][6] then [n][2]
-    double* d6 = nullptr; double* d2 = nullptr;
-    NB_CUDA(cudaMalloc(&d6, (size_t)c->n * 8 * sizeof(double)));
-    d2 = d6 + (size_t)c->n * 6;
-    rc = launch_snapshot_scatter(c->pos, c->vel, c->perm, c->n, d6, staticData2 ? d2 : nullptr, c->stream);
-    if (rc) { cudaFree(d6); return rc; }
+    // stage through persistent device scratch: [n][6] then [n][2] (the reference keeps the whole [T][n][6] history on the
+    // device, cuda/SimulationKernels.cu:204-249; here only one snapshot is ever resident)
+    if (!c->snap) NB_CUDA(cudaMalloc(&c->snap, (size_t)c->n * 8 * sizeof(double)));
+    double* d6 = c->snap; double* d2 = d6 + (size_t)c->n * 6;
+    rc = launch_snapshot_scatter(c->pos, c->vel, c->perm, c->n, d6, staticData2 ? d2 : nullptr, c->stream); if (rc) return rc;
     c->launches++;
-    cudaError_t e1 = cudaMemcpyAsync(particleData6, d6, (size_t)c->n * 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream);
-    cudaError_t e2 = staticData2 ? cudaMemcpyAsync(staticData2, d2, (size_t)c->n * 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream) : cudaSuccess;
-    cudaError_t e3 = cudaStreamSynchronize(c->stream);
-    cudaFree(d6);
-    NB_CUDA(e1); NB_CUDA(e2); NB_CUDA(e3);
+    NB_CUDA(cudaMemcpyAsync(particleData6, d6, (size_t)c->n * 6 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (staticData2) NB_CUDA(cudaMemcpyAsync(staticData2, d2, (size_t)c->n * 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
 
