@@ -90,7 +90,7 @@ def ncu_traffic_bytes(n, force, prec, world):
     (profiles/), valid for the default workload only; None otherwise."""
     if not (n == 1048576 and force == nbtest.PAIRWISE and prec == nbtest.FP32 and world == 1):
         return None
-    path = os.path.join(ROOT, "profiles", "r01_ncu_force_fp32_tma_frame_kernel.txt")
+    path = os.path.join(ROOT, "profiles", "r01_ncu_force_fp32_r4_production.txt")
     try:
         tot = 0.0
         for line in open(path):
@@ -315,8 +315,8 @@ def main():
                     "achieved": ach_int * SLOTS_PER_INTERACTION * 2 / 1e12,
                     "peak": peak_int * SLOTS_PER_INTERACTION * 2 / 1e12, "unit": "TFLOP/s",
                     "frac": ach_int / peak_int, "traffic": ncu_traffic_bytes(n, force, prec, world),
-                    "traffic_note": "DRAM bytes per launch from profiles/r01_ncu_force_fp32_tma_frame_kernel.txt; the "
-                                    "kernel's operands are 37.7 MB of packed tiles re-read from L2 by every CTA",
+                    "traffic_note": "DRAM bytes per launch from profiles/r01_ncu_force_fp32_r4_production.txt; the kernel's "
+                                    "operands are 42 MB of packed tiles re-read from L2 by every CTA + 50 MB of partial sums",
                     "achieved_Tint_per_s": ach_int / 1e12, "peak_Tint_per_s": peak_int / 1e12,
                     "kernel": "force_fp32 (per-GPU launch time from CUDA events on the context stream)",
                     "kernel_ms": fk_ms, "share_of_step": fk_ms / (t_step * 1e3),

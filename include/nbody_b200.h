@@ -23,7 +23,7 @@ extern "C" {
 #define NB_ERR_INVALID      1   /* bad argument / call order                                  */
 #define NB_ERR_CUDA         2   /* CUDA runtime error (replaces gpuErrchk's exit(), cuda/CudaUtils.cu:5-10) */
 #define NB_ERR_NCCL         3
-#define NB_ERR_UNSUPPORTED  4   /* reference-only method (BARNES_HUT, PAIRWISE_AVX2_FP32, VISUALIZATION)     */
+#define NB_ERR_UNSUPPORTED  4   /* reference-only method (BARNES_HUT, VISUALIZATION)                         */
 #define NB_ERR_NO_DEVICE    5   /* replaces the std::runtime_error of cuda/SimulationKernels.cu:35-50         */
 
 /* ---- enums: numeric values are the reference's enum-class values ------------------------------------------------ */
@@ -32,7 +32,8 @@ extern "C" {
 #define NB_INTEG_VELOCITY_VERLET  1
 /* ForceMethod, core/Forces.hpp:40-46 */
 #define NB_FORCE_PAIRWISE            0
-#define NB_FORCE_PAIRWISE_AVX2_FP32  1   /* reference-only: NB_ERR_UNSUPPORTED */
+#define NB_FORCE_PAIRWISE_AVX2_FP32  1   /* semantics of the reference's GPU kernel calculatePairwiseAccelOpt
+                                          * (cuda/ForceKernels.cu:173-204): Plummer softening r^2 + 1e-10, no cut-off */
 #define NB_FORCE_ADAPTIVE_MUTUAL     2
 #define NB_FORCE_BARNES_HUT          3   /* reference-only: NB_ERR_UNSUPPORTED */
 /* Arithmetic of the pair loop (new, optional; the reference GPU path is FP64 only) */

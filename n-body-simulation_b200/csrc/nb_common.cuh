@@ -55,8 +55,8 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 #define NB_CUDA(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return nb::cuda_fail(_e, #x, __FILE__, __LINE__); } while (0)
 
 // nb_force.cu
-int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, bool adaptive, int variant, cudaStream_t st);
-int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, bool adaptive, double avg_mass, cudaStream_t st);
+int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, int force_method, int variant, cudaStream_t st);
+int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st);
 int launch_potential_fp64(const double4* pos, double* pot, long npad, int ntiles, cudaStream_t st);
 int force_regs_info(char* buf, int len);
 int force_i_tiles_per_cta(int variant);

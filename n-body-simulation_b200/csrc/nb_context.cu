@@ -144,9 +144,9 @@ StepArrays arrays(nb_ctx* c) {
 int use_device(nb_ctx* c) { NB_CUDA(cudaSetDevice(c->device)); return NB_OK; }
 
 int check_force_method(int force) {
-    if (force == NB_FORCE_PAIRWISE || force == NB_FORCE_ADAPTIVE_MUTUAL) return NB_OK;
-    if (force == NB_FORCE_BARNES_HUT || force == NB_FORCE_PAIRWISE_AVX2_FP32)
-        return fail(NB_ERR_UNSUPPORTED, "forceMethod %d is reference-only (BARNES_HUT / PAIRWISE_AVX2_FP32 are not part of the B200 hot path)", force);
+    if (force == NB_FORCE_PAIRWISE || force == NB_FORCE_PAIRWISE_AVX2_FP32 || force == NB_FORCE_ADAPTIVE_MUTUAL) return NB_OK;
+    if (force == NB_FORCE_BARNES_HUT)
+        return fail(NB_ERR_UNSUPPORTED, "forceMethod %d (BARNES_HUT) is reference-only: not part of the B200 all-pairs hot path", force);
     return fail(NB_ERR_INVALID, "unknown forceMethod %d", force);
 }
 
@@ -176,13 +176,12 @@ int ensure_part(nb_ctx* c, int S_total) {
 }
 
 int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const float* pk, double* part) {
-    const bool adaptive = (c->force == NB_FORCE_ADAPTIVE_MUTUAL);
     int rc;
     if (c->precision == NB_PREC_FP32) {
         const int variant = c->force_variant == 0 ? 3 : c->force_variant;
-        rc = launch_force_fp32(pk, part, L, adaptive, variant, c->stream);
+        rc = launch_force_fp32(pk, part, L, c->force, variant, c->stream);
     } else {
-        rc = launch_force_fp64(pos, part, L, adaptive, c->avg_mass, c->stream);
+        rc = launch_force_fp64(pos, part, L, c->force, c->avg_mass, c->stream);
     }
     if (rc == NB_OK) c->launches++;
     return rc;

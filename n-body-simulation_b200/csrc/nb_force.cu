@@ -22,6 +22,13 @@ namespace nb {
 
 namespace {
 
+// Force law of a kernel instance (template parameter MODE)
+constexpr int kPairwise = 0;   // PAIRWISE: unsoftened, pairs with r^2 < 1e-10 skipped           (core/Forces.cpp:98-179)
+constexpr int kPlummer  = 1;   // PAIRWISE_AVX2_FP32 as the reference GPU runs it: s^2 = r^2 + 1e-10, no cut-off (cuda/ForceKernels.cu:173-204)
+constexpr int kAdaptive = 2;   // ADAPTIVE_MUTUAL                                              (core/Forces.cpp:301-387)
+#define IS_ADAPTIVE(m) ((m) == kAdaptive)
+#define IS_PLUMMER(m) ((m) == kPlummer)
+
 __device__ __forceinline__ float rsq_approx(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float lg2_approx(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float ex2_approx(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -76,11 +83,11 @@ __device__ __forceinline__ double pow23(double q) {
 // ------------------------------------------------------------------------------------------------------------------
 // Register-resident i-particles: R per thread, every value duplicated into both halves of a register pair so that one
 // packed instruction handles two j-particles.
-template <int R, bool ADAPTIVE>
+template <int R, int MODE>
 struct IState {
     float2 nxh[R], nyh[R], nzh[R];     // -(hi position)
     float2 nxl[R], nyl[R], nzl[R];     // -(lo position)
-    float2 mq[R];                      // m_i / (3 mean mass) (ADAPTIVE)
+    float2 mq[R];                      // m_i / (3 mean mass) (ADAPTIVE_MUTUAL)
     float2 ax[R], ay[R], az[R];        // FP32 partial sums (.x: even j, .y: odd j)
     double dax[R], day[R], daz[R];     // FP64 running sums
 };
@@ -90,8 +97,8 @@ struct IState {
 // FAR (only used in the i-block-relative frame of variant 2): the hi parts alone carry d to ~3e-7 and no pair of the
 // tile can be a self pair or inside the cut-off, so the lo adds and the compare/select are dropped:
 // 12 instead of 18 FP32-pipe operations per interaction.
-template <int R, bool ADAPTIVE, bool FAR>
-__device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* __restrict__ hi, const float* __restrict__ lo,
+template <int R, int MODE, bool FAR>
+__device__ __forceinline__ void interact4(IState<R, MODE>& S, const float* __restrict__ hi, const float* __restrict__ lo,
                                           const float* __restrict__ gmrow, const float* __restrict__ mqrow, int j4) {
     const float4 XH = reinterpret_cast<const float4*>(hi + 0 * kTJ)[j4];
     const float4 YH = reinterpret_cast<const float4*>(hi + 1 * kTJ)[j4];
@@ -104,7 +111,7 @@ __device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* _
         ZL = reinterpret_cast<const float4*>(lo + 2 * kTJ)[j4];
     }
     float4 MQ = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (ADAPTIVE) MQ = reinterpret_cast<const float4*>(mqrow)[j4];
+    if (IS_ADAPTIVE(MODE)) MQ = reinterpret_cast<const float4*>(mqrow)[j4];
 #pragma unroll
     for (int p = 0; p < 2; ++p) {
         const float2 xjh = p ? make_float2(XH.z, XH.w) : make_float2(XH.x, XH.y);
@@ -131,7 +138,7 @@ __device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* _
             r2 = __ffma2_rn(dy, dy, r2);
             r2 = __ffma2_rn(dx, dx, r2);
             float2 s2 = r2;
-            if (ADAPTIVE) {
+            if (IS_ADAPTIVE(MODE)) {
                 // eps^2 = max(eta^2 r^2 q^(2/3), eps_min^2), q = (m_i+m_j)/(3 mbar)   (core/Forces.cpp:353-356)
                 //  => s^2 = max(r^2 (1 + 1e-4 q^(2/3)), r^2 + 1e-8); q^(2/3) = 2^(2/3 log2 q) on the MUFU.
                 const float2 q = __fadd2_rn(mqj, S.mq[r]);
@@ -144,9 +151,12 @@ __device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* _
                 const float2 sb = __fadd2_rn(r2, make_float2(1e-8f, 1e-8f));
                 s2.x = fmaxf(sa.x, sb.x); s2.y = fmaxf(sa.y, sb.y);
             }
+            // PAIRWISE_AVX2_FP32 (GPU twin): Plummer softening eps^2 = 1e-10 instead of a cut-off; the self term is d = 0
+            // times a finite factor. Far tiles are >= 0.1 AU away (tile_is_far), where 1e-10 is below FP32 resolution.
+            if (IS_PLUMMER(MODE) && !FAR) s2 = __fadd2_rn(r2, make_float2(1e-10f, 1e-10f));
             float2 ri; ri.x = rsq_approx(s2.x); ri.y = rsq_approx(s2.y);
             // cut-off (also removes the self term, for which r2 == 0 exactly): core/Forces.cpp:135,144
-            if (!FAR) {
+            if (!FAR && !IS_PLUMMER(MODE)) {
                 ri.x = r2.x < 1e-10f ? 0.f : ri.x;
                 ri.y = r2.y < 1e-10f ? 0.f : ri.y;
             }
@@ -160,14 +170,14 @@ __device__ __forceinline__ void interact4(IState<R, ADAPTIVE>& S, const float* _
     }
 }
 
-template <int R, bool ADAPTIVE, bool FAR>
-__device__ __forceinline__ void tile_pass(IState<R, ADAPTIVE>& S, const float* __restrict__ hi, const float* __restrict__ lo,
+template <int R, int MODE, bool FAR>
+__device__ __forceinline__ void tile_pass(IState<R, MODE>& S, const float* __restrict__ hi, const float* __restrict__ lo,
                                           const float* __restrict__ gmrow, const float* __restrict__ mqrow) {
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
 #pragma unroll 2
         for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4)
-            interact4<R, ADAPTIVE, FAR>(S, hi, lo, gmrow, mqrow, j4);
+            interact4<R, MODE, FAR>(S, hi, lo, gmrow, mqrow, j4);
 #pragma unroll
         for (int r = 0; r < R; ++r) {      // flush 128 j's of FP32 partial sums into the FP64 accumulators
             S.dax[r] += (double)(S.ax[r].x + S.ax[r].y);
@@ -178,8 +188,8 @@ __device__ __forceinline__ void tile_pass(IState<R, ADAPTIVE>& S, const float* _
     }
 }
 
-template <int R, bool ADAPTIVE>
-__device__ __forceinline__ void init_acc(IState<R, ADAPTIVE>& S) {
+template <int R, int MODE>
+__device__ __forceinline__ void init_acc(IState<R, MODE>& S) {
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
@@ -187,8 +197,8 @@ __device__ __forceinline__ void init_acc(IState<R, ADAPTIVE>& S) {
     }
 }
 
-template <int R, bool ADAPTIVE>
-__device__ __forceinline__ void store_part(const IState<R, ADAPTIVE>& S, double* __restrict__ part, const ForceLaunch& L,
+template <int R, int MODE>
+__device__ __forceinline__ void store_part(const IState<R, MODE>& S, double* __restrict__ part, const ForceLaunch& L,
                                            int itile_first, int t, int s) {
     double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad;
 #pragma unroll
@@ -203,15 +213,15 @@ __device__ __forceinline__ int wrap_tile(int jt, int ntiles) { return jt >= ntil
 // ------------------------------------------------------------------------------------------------------------------
 // Variant 1 (simple, always accurate): global hi+lo coordinates for every tile, strict cut-off; j-tiles staged with
 // plain vector loads through registers, double-buffered, one barrier per tile. 18 FP32-pipe operations/interaction.
-template <int R, bool ADAPTIVE>
+template <int R, int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp32_ld_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
     __shared__ __align__(128) float sm[2][kTileFloats];
     const int t = threadIdx.x, s = blockIdx.y;
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
     const int itile_first = L.it0 + blockIdx.x * R;
-    IState<R, ADAPTIVE> S;
-    init_acc<R, ADAPTIVE>(S);
+    IState<R, MODE> S;
+    init_acc<R, MODE>(S);
 #pragma unroll
     for (int r = 0; r < R; ++r) {
         const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
@@ -222,7 +232,7 @@ force_fp32_ld_kernel(const float* __restrict__ pk, double* __restrict__ part, co
         v = -p[4 * kTJ]; S.nxl[r] = make_float2(v, v);
         v = -p[5 * kTJ]; S.nyl[r] = make_float2(v, v);
         v = -p[6 * kTJ]; S.nzl[r] = make_float2(v, v);
-        v = ADAPTIVE ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
+        v = IS_ADAPTIVE(MODE) ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
     }
     const float4* gsrc = reinterpret_cast<const float4*>(pk);
     constexpr int kV = 8 * kTJ / 4;                // rows 0..7 of the tile (the meta row is not needed here)
@@ -241,14 +251,14 @@ force_fp32_ld_kernel(const float* __restrict__ pk, double* __restrict__ part, co
             const float4* src = gsrc + (size_t)wrap_tile(L.jt0 + k + 1, L.ntiles) * (kTileFloats / 4);
             g0 = src[t]; g1 = src[t + kThreads];
         }
-        tile_pass<R, ADAPTIVE, false>(S, sm[b], sm[b] + 4 * kTJ, sm[b] + 3 * kTJ, sm[b] + 7 * kTJ);
+        tile_pass<R, MODE, false>(S, sm[b], sm[b] + 4 * kTJ, sm[b] + 3 * kTJ, sm[b] + 7 * kTJ);
         if (more) {
             reinterpret_cast<float4*>(sm[b ^ 1])[t] = g0;
             reinterpret_cast<float4*>(sm[b ^ 1])[t + kThreads] = g1;
         }
         __syncthreads();
     }
-    store_part<R, ADAPTIVE>(S, part, L, itile_first, t, s);
+    store_part<R, MODE>(S, part, L, itile_first, t, s);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -281,7 +291,7 @@ __device__ __forceinline__ void load_frame(CtaFrame& F, const float* __restrict_
     for (int c = 0; c < 3; ++c) { F.O[c] = 0.5f * F.lo[c] + 0.5f * F.hi[c]; F.half = fmaxf(F.half, 0.5f * (F.hi[c] - F.lo[c])); }
 }
 // meta: the j-tile's meta row (shared memory). CTA-uniform.
-__device__ __forceinline__ bool tile_is_far(const CtaFrame& F, const float* __restrict__ meta, float kappa) {
+__device__ __forceinline__ bool tile_is_far(const CtaFrame& F, const float* __restrict__ meta, float kappa, float min_gap2) {
     float g2 = 0.f, hj = 0.f;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
@@ -290,7 +300,7 @@ __device__ __forceinline__ bool tile_is_far(const CtaFrame& F, const float* __re
         hj = fmaxf(hj, 0.5f * (meta[3 + c] - meta[c]));
     }
     const float thr = kappa * (F.half + hj);
-    return (g2 > thr * thr) && (g2 > 1e-8f);
+    return (g2 > thr * thr) && (g2 > min_gap2);
 }
 // (h, l) = two-float value of (xh + xl) - O: TwoSum(xh, -O) is error free, the low words are then folded in.
 __device__ __forceinline__ void rel_two(float xh, float xl, float O, float& h, float& l) {
@@ -316,7 +326,7 @@ __device__ __forceinline__ void transform_tile(const float* __restrict__ raw, fl
     }
 }
 
-template <int R, bool ADAPTIVE>
+template <int R, int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
     __shared__ __align__(128) float raw[kStages][kTileFloats];
@@ -341,8 +351,8 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
     }
     CtaFrame F;
     load_frame<R>(F, pk, itile_first);
-    IState<R, ADAPTIVE> S;
-    init_acc<R, ADAPTIVE>(S);
+    IState<R, MODE> S;
+    init_acc<R, MODE>(S);
 #pragma unroll
     for (int r = 0; r < R; ++r) {      // own i-particles in the CTA frame, as two-float values
         const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
@@ -350,12 +360,12 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
         rel_two(p[0 * kTJ], p[4 * kTJ], F.O[0], h, l); S.nxh[r] = make_float2(-h, -h); S.nxl[r] = make_float2(-l, -l);
         rel_two(p[1 * kTJ], p[5 * kTJ], F.O[1], h, l); S.nyh[r] = make_float2(-h, -h); S.nyl[r] = make_float2(-l, -l);
         rel_two(p[2 * kTJ], p[6 * kTJ], F.O[2], h, l); S.nzh[r] = make_float2(-h, -h); S.nzl[r] = make_float2(-l, -l);
-        const float v = ADAPTIVE ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
+        const float v = IS_ADAPTIVE(MODE) ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
     }
     bool far_cur = false;
     if (cnt > 0) {
         mbar_wait(&full[0], 0u);
-        far_cur = tile_is_far(F, raw[0] + kMetaRow * kTJ, L.kappa);
+        far_cur = tile_is_far(F, raw[0] + kMetaRow * kTJ, L.kappa, IS_PLUMMER(MODE) ? 1e-2f : 1e-8f);
         if (far_cur) transform_tile<true>(raw[0], T[0], F, t); else transform_tile<false>(raw[0], T[0], F, t);
     }
     __syncthreads();
@@ -365,13 +375,13 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
         if (q + 1 < cnt) {                 // re-express the next tile while this one is being computed
             const int bn = (q + 1) % kStages;
             mbar_wait(&full[bn], (uint32_t)(((q + 1) / kStages) & 1));
-            far_next = tile_is_far(F, raw[bn] + kMetaRow * kTJ, L.kappa);
+            far_next = tile_is_far(F, raw[bn] + kMetaRow * kTJ, L.kappa, IS_PLUMMER(MODE) ? 1e-2f : 1e-8f);
             float* Tn = T[(q + 1) & 1];
             if (far_next) transform_tile<true>(raw[bn], Tn, F, t); else transform_tile<false>(raw[bn], Tn, F, t);
         }
         const float* Tc = T[q & 1];
-        if (far_cur) tile_pass<R, ADAPTIVE, true>(S, Tc, Tc + 3 * kTJ, raw[b] + 3 * kTJ, raw[b] + 7 * kTJ);
-        else         tile_pass<R, ADAPTIVE, false>(S, Tc, Tc + 3 * kTJ, raw[b] + 3 * kTJ, raw[b] + 7 * kTJ);
+        if (far_cur) tile_pass<R, MODE, true>(S, Tc, Tc + 3 * kTJ, raw[b] + 3 * kTJ, raw[b] + 7 * kTJ);
+        else         tile_pass<R, MODE, false>(S, Tc, Tc + 3 * kTJ, raw[b] + 3 * kTJ, raw[b] + 7 * kTJ);
         __syncthreads();                   // every warp is done with raw[b] and T[q&1]; T[(q+1)&1] is complete
         if (t == 0 && q + kStages < cnt) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -380,7 +390,7 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
         }
         far_cur = far_next;
     }
-    store_part<R, ADAPTIVE>(S, part, L, itile_first, t, s);
+    store_part<R, MODE>(S, part, L, itile_first, t, s);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -396,14 +406,14 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
 //     directions (pair terms 100x larger than their sum): those terms are now exact to ~1e-15 instead of ~1e-7.
 // Per j-tile the four i-tiles of the CTA are classified independently (bit r of `mask` = i-tile r is far).
 constexpr int kR4 = 4;
-constexpr int kFarFloats = 4 * kTJ;                         // rows k x', k y', k z', k  (PAIRWISE)  |  x', y', z', -  (ADAPTIVE)
+constexpr int kFarFloats = 4 * kTJ;                         // rows k x', k y', k z', k  (PAIRWISE)  |  x', y', z', -  (ADAPTIVE_MUTUAL)
 constexpr int kXfFloats = kFarFloats + 3 * kTJ * 2;         // + three rows of doubles (x', y', z') for the FP64 near path
 constexpr size_t kR4SmemBytes = (size_t)kStages * kTileBytes + 2 * (size_t)kXfFloats * 4 + (size_t)kR4 * 3 * kTJ * 8 + 32 + kStages * 8;
 
-template <bool ADAPTIVE>
+template <int MODE>
 struct IState4 {
     float2 nx[kR4], ny[kR4], nz[kR4];   // -(x'_i) duplicated in both halves (CTA frame)
-    float2 mq[kR4];                     // m_i / (3 mean mass) (ADAPTIVE)
+    float2 mq[kR4];                     // m_i / (3 mean mass) (ADAPTIVE_MUTUAL)
     float2 ax[kR4], ay[kR4], az[kR4];   // FP32 partial sums
 };
 
@@ -414,16 +424,16 @@ struct IState4 {
 //   ADAPTIVE: plain frame, G m_j and m_j/(3 mbar) from the raw tile.
 //   MASKED: i-tiles whose bit in `mask` is clear are in the near field of this j-tile and are handled in FP64
 //   elsewhere; their contribution is switched off here (the select also removes the inf of a self pair).
-template <bool ADAPTIVE, bool MASKED>
-__device__ __forceinline__ void far_j4(IState4<ADAPTIVE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
+template <int MODE, bool MASKED>
+__device__ __forceinline__ void far_j4(IState4<MODE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
                                        int j4, uint32_t mask) {
     const float4 X = reinterpret_cast<const float4*>(Tf + 0 * kTJ)[j4];
     const float4 Y = reinterpret_cast<const float4*>(Tf + 1 * kTJ)[j4];
     const float4 Z = reinterpret_cast<const float4*>(Tf + 2 * kTJ)[j4];
-    const float4 K = ADAPTIVE ? reinterpret_cast<const float4*>(raw + 3 * kTJ)[j4]       // G m_j
+    const float4 K = IS_ADAPTIVE(MODE) ? reinterpret_cast<const float4*>(raw + 3 * kTJ)[j4]       // G m_j
                               : reinterpret_cast<const float4*>(Tf + 3 * kTJ)[j4];       // k_j
     float4 MQ = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (ADAPTIVE) MQ = reinterpret_cast<const float4*>(raw + 7 * kTJ)[j4];
+    if (IS_ADAPTIVE(MODE)) MQ = reinterpret_cast<const float4*>(raw + 7 * kTJ)[j4];
 #pragma unroll
     for (int p = 0; p < 2; ++p) {
         const float2 xj = p ? make_float2(X.z, X.w) : make_float2(X.x, X.y);
@@ -434,7 +444,7 @@ __device__ __forceinline__ void far_j4(IState4<ADAPTIVE>& S, const float* __rest
 #pragma unroll
         for (int r = 0; r < kR4; ++r) {
             float2 dx, dy, dz;
-            if (!ADAPTIVE) {
+            if (!IS_ADAPTIVE(MODE)) {
                 dx = __ffma2_rn(S.nx[r], kj, xj); dy = __ffma2_rn(S.ny[r], kj, yj); dz = __ffma2_rn(S.nz[r], kj, zj);
             } else {
                 dx = __fadd2_rn(xj, S.nx[r]); dy = __fadd2_rn(yj, S.ny[r]); dz = __fadd2_rn(zj, S.nz[r]);
@@ -443,7 +453,7 @@ __device__ __forceinline__ void far_j4(IState4<ADAPTIVE>& S, const float* __rest
             r2 = __ffma2_rn(dy, dy, r2);
             r2 = __ffma2_rn(dx, dx, r2);
             float2 s2 = r2;
-            if (ADAPTIVE) {
+            if (IS_ADAPTIVE(MODE)) {
                 const float2 q = __fadd2_rn(mqj, S.mq[r]);
                 float2 lg; lg.x = lg2_approx(q.x); lg.y = lg2_approx(q.y);
                 const float kLog2Eta2 = -13.287712379549449f;
@@ -460,7 +470,7 @@ __device__ __forceinline__ void far_j4(IState4<ADAPTIVE>& S, const float* __rest
             }
             const float2 ri2 = __fmul2_rn(ri, ri);
             float2 sc;
-            if (!ADAPTIVE) sc = __fmul2_rn(ri, ri2);
+            if (!IS_ADAPTIVE(MODE)) sc = __fmul2_rn(ri, ri2);
             else { sc = __fmul2_rn(kj, ri); sc = __fmul2_rn(sc, ri2); }
             S.ax[r] = __ffma2_rn(sc, dx, S.ax[r]); S.ay[r] = __ffma2_rn(sc, dy, S.ay[r]); S.az[r] = __ffma2_rn(sc, dz, S.az[r]);
         }
@@ -469,14 +479,14 @@ __device__ __forceinline__ void far_j4(IState4<ADAPTIVE>& S, const float* __rest
 
 // whole tile, far field; FP32 partial sums are flushed into the FP64 sums in shared memory (thread-private slots)
 // every 128 j. PAIRWISE sums are in units of G0 (mass-scaled frame).
-template <bool ADAPTIVE, bool MASKED>
-__device__ __forceinline__ void far_tile(IState4<ADAPTIVE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
+template <int MODE, bool MASKED>
+__device__ __forceinline__ void far_tile(IState4<MODE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
                                          double* __restrict__ dacc, int t, float g0, uint32_t mask) {
-    const float unit = ADAPTIVE ? 1.f : g0;
+    const float unit = IS_ADAPTIVE(MODE) ? 1.f : g0;
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
 #pragma unroll 2
-        for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4) far_j4<ADAPTIVE, MASKED>(S, Tf, raw, j4, mask);
+        for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4) far_j4<MODE, MASKED>(S, Tf, raw, j4, mask);
 #pragma unroll
         for (int r = 0; r < kR4; ++r) {
             double* d = dacc + (size_t)r * 3 * kTJ + t;
@@ -489,7 +499,7 @@ __device__ __forceinline__ void far_tile(IState4<ADAPTIVE>& S, const float* __re
 }
 
 // whole tile, FP64 near field, ONE i-particle (i-tile `itile`, lane t), CTA frame origin O
-template <bool ADAPTIVE>
+template <int MODE>
 __device__ __forceinline__ void near_tile64(const float* __restrict__ pk, int itile, int t, const float* __restrict__ O,
                                             const double* __restrict__ Td, const float* __restrict__ raw,
                                             double* __restrict__ d3 /* dacc + r*3*kTJ + t */) {
@@ -497,7 +507,7 @@ __device__ __forceinline__ void near_tile64(const float* __restrict__ pk, int it
     const double xi = ((double)p[0 * kTJ] - (double)O[0]) + (double)p[4 * kTJ];
     const double yi = ((double)p[1 * kTJ] - (double)O[1]) + (double)p[5 * kTJ];
     const double zi = ((double)p[2 * kTJ] - (double)O[2]) + (double)p[6 * kTJ];
-    const double mqi = ADAPTIVE ? (double)p[7 * kTJ] : 0.0;
+    const double mqi = IS_ADAPTIVE(MODE) ? (double)p[7 * kTJ] : 0.0;
     double ax = 0.0, ay = 0.0, az = 0.0;
 #pragma unroll 4
     for (int j = 0; j < kTJ; ++j) {
@@ -505,12 +515,13 @@ __device__ __forceinline__ void near_tile64(const float* __restrict__ pk, int it
         const double gm = (double)raw[3 * kTJ + j] + (double)raw[kGmLoRow * kTJ + j];
         const double r2 = dx * dx + dy * dy + dz * dz;
         double s2 = r2;
-        if (ADAPTIVE) {
+        if (IS_ADAPTIVE(MODE)) {
             const double w = pow23(mqi + (double)raw[7 * kTJ + j]);
             s2 = fmax(fma(r2 * w, 1e-4, r2), r2 + 1e-8);
         }
+        if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
         double sc = gm_inv_r3(s2, gm);
-        sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;      // cut-off and self pair
+        if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off and self pair
         ax = fma(sc, dx, ax); ay = fma(sc, dy, ay); az = fma(sc, dz, az);
     }
     d3[0] += ax; d3[kTJ] += ay; d3[2 * kTJ] += az;
@@ -519,7 +530,7 @@ __device__ __forceinline__ void near_tile64(const float* __restrict__ pk, int it
 // per-i-tile bounding boxes of the CTA: thread r (< kR4) owns box r and classifies the j-tiles for it
 struct IBox1 { float lo[3], hi[3]; };
 
-template <bool ADAPTIVE>
+template <int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -556,7 +567,7 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
         for (int c = 0; c < 3; ++c) { B.lo[c] = __ldg(m + c); B.hi[c] = __ldg(m + 3 + c); }
     }
     const float inv_g0 = 1.f / L.g0;
-    IState4<ADAPTIVE> S;
+    IState4<MODE> S;
 #pragma unroll
     for (int r = 0; r < kR4; ++r) {
         const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
@@ -564,7 +575,7 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
         v = -((p[0 * kTJ] - F.O[0]) + p[4 * kTJ]); S.nx[r] = make_float2(v, v);
         v = -((p[1 * kTJ] - F.O[1]) + p[5 * kTJ]); S.ny[r] = make_float2(v, v);
         v = -((p[2 * kTJ] - F.O[2]) + p[6 * kTJ]); S.nz[r] = make_float2(v, v);
-        v = ADAPTIVE ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
+        v = IS_ADAPTIVE(MODE) ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
         S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
     }
     // classify (thread r < 4) and re-express (thread t <-> particle t) tile q into buffer q & 1
@@ -582,11 +593,11 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
                 hj = fmaxf(hj, 0.5f * (meta[3 + c] - meta[c]));
             }
             const float thr = L.kappa * (F.half + hj);          // F.half: half-extent of the whole i-block (frame size)
-            flags[(q & 1) * 4 + t] = ((g2 > thr * thr) && (g2 > 1e-8f)) ? 1u : 0u;
+            flags[(q & 1) * 4 + t] = ((g2 > thr * thr) && (g2 > (IS_PLUMMER(MODE) ? 1e-2f : 1e-8f))) ? 1u : 0u;
         }
         float kj = 1.f;     // PAIRWISE: k_j = sqrt(G0 / (G m_j)); massless particles get a huge finite k, their r'^2 overflows
                             // to +inf, rsqrt gives 0 and they contribute exactly nothing
-        if (!ADAPTIVE) { kj = rsq_approx(fmaxf(rw[3 * kTJ + t] * inv_g0, 1e-30f)); Tf[3 * kTJ + t] = kj; }
+        if (!IS_ADAPTIVE(MODE)) { kj = rsq_approx(fmaxf(rw[3 * kTJ + t] * inv_g0, 1e-30f)); Tf[3 * kTJ + t] = kj; }
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             const float xh = rw[c * kTJ + t], xl = rw[(4 + c) * kTJ + t];
@@ -608,12 +619,12 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
         const float* Tf = T + (q & 1) * kXfFloats;
         const double* Td = reinterpret_cast<const double*>(Tf + kFarFloats);
         if (mask == 0xFu) {
-            far_tile<ADAPTIVE, false>(S, Tf, rw, dacc, t, L.g0, mask);
+            far_tile<MODE, false>(S, Tf, rw, dacc, t, L.g0, mask);
         } else {
-            if (mask != 0u) far_tile<ADAPTIVE, true>(S, Tf, rw, dacc, t, L.g0, mask);
+            if (mask != 0u) far_tile<MODE, true>(S, Tf, rw, dacc, t, L.g0, mask);
 #pragma unroll 1
             for (int r = 0; r < kR4; ++r)
-                if (!((mask >> r) & 1u)) near_tile64<ADAPTIVE>(pk, itile_first + r, t, F.O, Td, rw, dacc + (size_t)r * 3 * kTJ + t);
+                if (!((mask >> r) & 1u)) near_tile64<MODE>(pk, itile_first + r, t, F.O, Td, rw, dacc + (size_t)r * 3 * kTJ + t);
         }
         __syncthreads();                       // all warps done with raw[b], T[q&1], flags[q&1]; tile q+1 is prepared
         if (t == 0 && q + kStages < cnt) {
@@ -634,7 +645,7 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
 // FP64 mode. Tiles of 256 double4 (x,y,z,m) straight from the master array; R = 2 i-particles per thread.
 constexpr int kR64 = 2;
 
-template <bool ADAPTIVE>
+template <int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, const ForceLaunch L, double inv3mbar) {
     __shared__ __align__(16) double4 sm[2][kTJ];
@@ -658,21 +669,22 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
         for (int j = 0; j < kTJ; ++j) {
             const double4 pj = sm[b][j];
             const double gm = kG * pj.w;
-            const double mqj = ADAPTIVE ? pj.w * inv3mbar : 0.0;
+            const double mqj = IS_ADAPTIVE(MODE) ? pj.w * inv3mbar : 0.0;
 #pragma unroll
             for (int r = 0; r < kR64; ++r) {
                 const double dx = pj.x - xi[r], dy = pj.y - yi[r], dz = pj.z - zi[r];
                 const double r2 = dx * dx + dy * dy + dz * dz;
                 double s2 = r2;
-                if (ADAPTIVE) {
+                if (IS_ADAPTIVE(MODE)) {
                     // eps^2 = max(eta^2 r^2 q^(2/3), eps_min^2) (core/Forces.cpp:353-356)
                     const double w = pow23(mqi[r] + mqj);
                     s2 = fmax(fma(r2 * w, 1e-4, r2), r2 + 1e-8);
                 }
+                if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                  // cuda/ForceKernels.cu:186
                 double sc = gm_inv_r3(s2, gm);
                 // r2 >= 0, so the integer order of the bit patterns is the floating-point order: the cut-off test
                 // (core/Forces.cpp:144) runs on the integer pipe instead of the FP64 pipe.
-                sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;
+                if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;
                 ax[r] = fma(sc, dx, ax[r]); ay[r] = fma(sc, dy, ay[r]); az[r] = fma(sc, dz, az[r]);
             }
         }
@@ -738,43 +750,50 @@ constexpr int kR32 = 2;   // i-particles per thread of variants 1 and 2
 
 int force_i_tiles_per_cta(int variant) { return variant == 3 ? kR4 : kR32; }
 
-int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, bool adaptive, int variant, cudaStream_t st) {
-    if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
+template <int MODE>
+int launch_fp32_mode(const float* pk, double* part, const ForceLaunch& L, int variant, cudaStream_t st) {
     if (variant == 3) {
         if (L.nit % kR4 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR4);
         static bool attr_set[64] = {};
         int dev = 0; NB_CUDA(cudaGetDevice(&dev));
         if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-            NB_CUDA(cudaFuncSetAttribute(force_fp32_r4_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kR4SmemBytes));
-            NB_CUDA(cudaFuncSetAttribute(force_fp32_r4_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kR4SmemBytes));
+            NB_CUDA(cudaFuncSetAttribute(force_fp32_r4_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kR4SmemBytes));
             attr_set[dev] = true;
         }
         dim3 grid(L.nit / kR4, L.S), block(kThreads);
-        if (adaptive) force_fp32_r4_kernel<true><<<grid, block, kR4SmemBytes, st>>>(pk, part, L);
-        else          force_fp32_r4_kernel<false><<<grid, block, kR4SmemBytes, st>>>(pk, part, L);
-        NB_CUDA(cudaGetLastError());
-        return NB_OK;
-    }
-    if (L.nit % kR32 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR32);
-    dim3 grid(L.nit / kR32, L.S), block(kThreads);
-    if (variant == 2) {
-        if (adaptive) force_fp32_tma_kernel<kR32, true><<<grid, block, 0, st>>>(pk, part, L);
-        else          force_fp32_tma_kernel<kR32, false><<<grid, block, 0, st>>>(pk, part, L);
+        force_fp32_r4_kernel<MODE><<<grid, block, kR4SmemBytes, st>>>(pk, part, L);
     } else {
-        if (adaptive) force_fp32_ld_kernel<kR32, true><<<grid, block, 0, st>>>(pk, part, L);
-        else          force_fp32_ld_kernel<kR32, false><<<grid, block, 0, st>>>(pk, part, L);
+        if (L.nit % kR32 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR32);
+        dim3 grid(L.nit / kR32, L.S), block(kThreads);
+        if (variant == 2) force_fp32_tma_kernel<kR32, MODE><<<grid, block, 0, st>>>(pk, part, L);
+        else              force_fp32_ld_kernel<kR32, MODE><<<grid, block, 0, st>>>(pk, part, L);
     }
     NB_CUDA(cudaGetLastError());
     return NB_OK;
 }
 
-int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, bool adaptive, double avg_mass, cudaStream_t st) {
+// force_method: NB_FORCE_PAIRWISE (0), NB_FORCE_PAIRWISE_AVX2_FP32 (1), NB_FORCE_ADAPTIVE_MUTUAL (2) == kernel MODE
+int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, int force_method, int variant, cudaStream_t st) {
+    if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
+    switch (force_method) {
+        case kPairwise: return launch_fp32_mode<kPairwise>(pk, part, L, variant, st);
+        case kPlummer:  return launch_fp32_mode<kPlummer>(pk, part, L, variant, st);
+        case kAdaptive: return launch_fp32_mode<kAdaptive>(pk, part, L, variant, st);
+    }
+    return fail(NB_ERR_INVALID, "force: unknown method %d", force_method);
+}
+
+int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st) {
     if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
     if (L.nit % kR64 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR64);
     dim3 grid(L.nit / kR64, L.S), block(kThreads);
-    const double inv3mbar = adaptive ? 1.0 / (3.0 * avg_mass) : 0.0;
-    if (adaptive) force_fp64_kernel<true><<<grid, block, 0, st>>>(pos, part, L, inv3mbar);
-    else          force_fp64_kernel<false><<<grid, block, 0, st>>>(pos, part, L, inv3mbar);
+    const double inv3mbar = force_method == kAdaptive ? 1.0 / (3.0 * avg_mass) : 0.0;
+    switch (force_method) {
+        case kPairwise: force_fp64_kernel<kPairwise><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
+        case kPlummer:  force_fp64_kernel<kPlummer><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
+        case kAdaptive: force_fp64_kernel<kAdaptive><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
+        default: return fail(NB_ERR_INVALID, "force: unknown method %d", force_method);
+    }
     NB_CUDA(cudaGetLastError());
     return NB_OK;
 }
@@ -787,11 +806,10 @@ int launch_potential_fp64(const double4* pos, double* pot, long npad, int ntiles
 }
 
 int force_regs_info(char* buf, int len) {
-    return snprintf(buf, len, "fp32_r4:%d fp32_r4_adaptive:%d fp32_ld:%d fp32_ld_adaptive:%d fp32_tma:%d fp32_tma_adaptive:%d fp64:%d fp64_adaptive:%d",
-                    regs_of(force_fp32_r4_kernel<false>), regs_of(force_fp32_r4_kernel<true>),
-                    regs_of(force_fp32_ld_kernel<kR32, false>), regs_of(force_fp32_ld_kernel<kR32, true>),
-                    regs_of(force_fp32_tma_kernel<kR32, false>), regs_of(force_fp32_tma_kernel<kR32, true>),
-                    regs_of(force_fp64_kernel<false>), regs_of(force_fp64_kernel<true>));
+    return snprintf(buf, len, "fp32_r4:%d fp32_r4_plummer:%d fp32_r4_adaptive:%d fp32_tma:%d fp32_ld:%d fp64:%d fp64_adaptive:%d",
+                    regs_of(force_fp32_r4_kernel<kPairwise>), regs_of(force_fp32_r4_kernel<kPlummer>), regs_of(force_fp32_r4_kernel<kAdaptive>),
+                    regs_of(force_fp32_tma_kernel<kR32, kPairwise>), regs_of(force_fp32_ld_kernel<kR32, kPairwise>),
+                    regs_of(force_fp64_kernel<kPairwise>), regs_of(force_fp64_kernel<kAdaptive>));
 }
 
 } // namespace nb

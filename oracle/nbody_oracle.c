@@ -56,6 +56,27 @@ double nbo_average_mass(long n, const double* pm) {
     return total / (double)n;
 }
 
+/* calculatePairwiseAccelOpt — simulator/cuda/ForceKernels.cu:173-204: what forceMethod PAIRWISE_AVX2_FP32 runs on the
+ * reference's GPU path (Plummer softening r^2 + 1e-10, no cut-off, self term included and equal to zero, float rsqrt
+ * refined by one Newton step in double). The CPU twin (Forces.cpp:202-296) drops tile tails and keeps the unrefined
+ * 12-bit rsqrt, so the GPU kernel is the parity target. Serial j order as in the kernel. */
+static void plummer_row(const double* pm, long n, long i, double out[3]) {
+    const double ix = pm[4 * i], iy = pm[4 * i + 1], iz = pm[4 * i + 2];
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (long j = 0; j < n; ++j) {
+        const double dx = pm[4 * j] - ix, dy = pm[4 * j + 1] - iy, dz = pm[4 * j + 2] - iz;
+        const double r2 = dx * dx + dy * dy + dz * dz + 1e-10;                 /* :186 */
+        if (r2 > 0.0) {                                                        /* :188 */
+            const float rinv_f = 1.0f / sqrtf((float)r2);                      /* :189 rsqrtf((float)r2) */
+            double rinv = (double)rinv_f;
+            rinv = rinv * (1.5 - 0.5 * r2 * rinv * rinv);                      /* :191 Newton step */
+            const double f = NBO_G * pm[4 * j + 3] * (rinv * rinv * rinv);     /* :193-194 */
+            ax += f * dx; ay += f * dy; az += f * dz;                          /* :196-198 */
+        }
+    }
+    out[0] = ax; out[1] = ay; out[2] = az;
+}
+
 /* One i-particle against the j-range [j0,j1): the inner loops of
  *   pairwiseAcceleration               simulator/core/Forces.cpp:126-160
  *   pairwiseAccelerationAdaptiveMutual simulator/core/Forces.cpp:332-377
@@ -86,10 +107,15 @@ static void tile_partial(const double* pm, long i, long j0, long j1, int adaptiv
 }
 
 /* calculateForces dispatch — simulator/core/Forces.cpp:67-83. Only PAIRWISE (0) and ADAPTIVE_MUTUAL (2) are on
- * the hot path; other enum values return non-zero. accel3 is n x (ax,ay,az) (Accelerations, Forces.hpp:5-37).
+ * the hot path, PAIRWISE_AVX2_FP32 (1) follows the reference GPU kernel (plummer_row); BARNES_HUT returns non-zero. accel3 is n x (ax,ay,az) (Accelerations, Forces.hpp:5-37).
  * Each i is owned by one thread (as in the reference's omp-for over i-tiles) so the result does not depend on
  * the thread count. */
 int nbo_forces(long n, const double* pm, int method, double* accel3) {
+    if (method == NBO_FORCE_PAIRWISE_AVX2_FP32) {
+        #pragma omp parallel for schedule(dynamic, 16)
+        for (long i = 0; i < n; ++i) plummer_row(pm, n, i, accel3 + 3 * i);
+        return 0;
+    }
     if (method != NBO_FORCE_PAIRWISE && method != NBO_FORCE_ADAPTIVE_MUTUAL) return 1;
     const int adaptive = (method == NBO_FORCE_ADAPTIVE_MUTUAL);
     const double avg = adaptive ? nbo_average_mass(n, pm) : 0.0;   /* Forces.cpp:309 */
@@ -112,6 +138,11 @@ int nbo_forces(long n, const double* pm, int method, double* accel3) {
 /* Sampled-subset arbiter for N too large for the full O(N^2) CPU pass (SURVEY.md §8c last row): the same
  * per-pair arithmetic as tile_partial, accumulated in long double, for the i-indices listed in idx. */
 int nbo_forces_subset(long n, const double* pm, int method, long n_idx, const long* idx, double* accel3) {
+    if (method == NBO_FORCE_PAIRWISE_AVX2_FP32) {
+        #pragma omp parallel for schedule(dynamic, 1)
+        for (long k = 0; k < n_idx; ++k) plummer_row(pm, n, idx[k], accel3 + 3 * k);
+        return 0;
+    }
     if (method != NBO_FORCE_PAIRWISE && method != NBO_FORCE_ADAPTIVE_MUTUAL) return 1;
     const int adaptive = (method == NBO_FORCE_ADAPTIVE_MUTUAL);
     const double avg = adaptive ? nbo_average_mass(n, pm) : 0.0;

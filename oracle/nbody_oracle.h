@@ -5,6 +5,7 @@
 extern "C" {
 #endif
 #define NBO_FORCE_PAIRWISE 0
+#define NBO_FORCE_PAIRWISE_AVX2_FP32 1
 #define NBO_FORCE_ADAPTIVE_MUTUAL 2
 #define NBO_INTEG_EULER 0
 #define NBO_INTEG_VELOCITY_VERLET 1

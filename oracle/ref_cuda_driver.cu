@@ -2,10 +2,17 @@
 // FP64 CUDA kernels (cuda/ForceKernels.cu, IntegrationKernels.cu, BenchmarkKernels.cu, CudaUtils.cu, Constants.cu,
 // BHKernels2.cu), compiled unmodified for sm_100a by `make -C oracle refcuda`, driven through the reference's
 // runBenchmarkOnGPU exactly as System::runGPUBenchmark does (core/System.cpp:197-207). Prints one JSON line.
-//   usage: ref_cuda_bench <n> <steps> <force 0|2> <block_size (0 = reference heuristic)>
+//   usage: ref_cuda_bench <n> <steps> <force 0|1|2> <block_size (0 = reference heuristic)>
+//          ref_cuda_bench force <in.nbin> <out.f64> <force 0|1|2>   one launchForceKernel (cuda/ForceKernels.cu:208-232) on the
+//                         particles of a binary snapshot; writes n x (ax,ay,az,0) doubles — golden outputs of the reference's
+//                         own GPU kernels for the parity tests.
 #include "System.hpp"
 #include "Initializer.hpp"
 #include "BenchmarkKernels.h"
+#include "ForceKernels.cuh"
+#include <cstring>
+#include <fstream>
+#include <vector>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -13,7 +20,32 @@
 // the viewer entry point System.cpp references; there is no graphics stack here
 extern "C" void runVisualizationOnGPU(Particles&, IntegrationMethod, ForceMethod, double, int, double, int) { std::abort(); }
 
+static int force_mode(int argc, char** argv) {
+    if (argc < 5) { std::fprintf(stderr, "usage: ref_cuda_bench force <in.nbin> <out.f64> <method>\n"); return 2; }
+    std::ifstream f(argv[2], std::ios::binary);
+    char magic[8]; unsigned long long n = 0;
+    f.read(magic, 8); f.read(reinterpret_cast<char*>(&n), 8);
+    if (!f || std::memcmp(magic, "NBIN0001", 8) != 0) { std::fprintf(stderr, "not a NBIN0001 snapshot\n"); return 2; }
+    std::vector<double4> pos(n);
+    f.read(reinterpret_cast<char*>(pos.data()), (std::streamsize)(n * sizeof(double4)));
+    const ForceMethod method = static_cast<ForceMethod>(std::atoi(argv[4]));
+    double avg = 0.0; for (auto& p : pos) avg += p.w; avg /= (double)n;          // cuda/BenchmarkKernels.cu:59-65
+    double4 *d_pos = nullptr, *d_acc = nullptr;
+    gpuErrchk(cudaMalloc(&d_pos, n * sizeof(double4))); gpuErrchk(cudaMalloc(&d_acc, n * sizeof(double4)));
+    gpuErrchk(cudaMemcpy(d_pos, pos.data(), n * sizeof(double4), cudaMemcpyHostToDevice));
+    const int block = 256;                                                        // core/System.hpp:98
+    launchForceKernel(method, calculateGrid((int)n, block), block, block * sizeof(double4), 0, d_pos, d_acc, avg, (int)n);
+    gpuErrchk(cudaDeviceSynchronize());
+    std::vector<double4> acc(n);
+    gpuErrchk(cudaMemcpy(acc.data(), d_acc, n * sizeof(double4), cudaMemcpyDeviceToHost));
+    std::ofstream o(argv[3], std::ios::binary);
+    o.write(reinterpret_cast<const char*>(acc.data()), (std::streamsize)(n * sizeof(double4)));
+    cudaFree(d_pos); cudaFree(d_acc);
+    return o ? 0 : 1;
+}
+
 int main(int argc, char** argv) {
+    if (argc > 1 && std::strcmp(argv[1], "force") == 0) return force_mode(argc, argv);
     const int n = argc > 1 ? std::atoi(argv[1]) : 65536;
     const int steps = argc > 2 ? std::atoi(argv[2]) : 5;
     const ForceMethod force = static_cast<ForceMethod>(argc > 3 ? std::atoi(argv[3]) : 0);

@@ -114,6 +114,22 @@ def test_edge_cases(oracle):
     np.testing.assert_allclose(np.linalg.norm(a[0]), nbtest.G * 1.0 / 25.0, rtol=1e-15)
 
 
+def test_plummer_restatement(oracle):
+    """Method 1 = the reference GPU kernel calculatePairwiseAccelOpt: Plummer eps^2 = 1e-10, no cut-off."""
+    pm, _ = nbtest.gen_random(400, seed=2)
+    a = oracle.forces(pm, nbtest.AVX2)
+    d = pm[None, :, :3] - pm[:, None, :3]
+    r2 = (d * d).sum(2) + 1e-10
+    exact = (nbtest.G * pm[None, :, 3:4] * d / (r2 ** 1.5)[:, :, None]).sum(1)
+    assert nbtest.rel_err(a, exact).max() < 1e-12
+    # far from the cut-off it coincides with PAIRWISE
+    assert nbtest.rel_err(a, oracle.forces(pm, PAIRWISE)).max() < 1e-3
+    two = np.array([[0, 0, 0, 1.0], [3e-6, 0, 0, 1.0]])                     # below the PAIRWISE cut-off
+    assert np.all(oracle.forces(two, PAIRWISE) == 0.0) and abs(oracle.forces(two, nbtest.AVX2)[0, 0]) > 1e9
+    idx = np.array([5, 17, 399])
+    assert np.array_equal(oracle.forces_subset(pm, nbtest.AVX2, idx), a[idx])
+
+
 def test_thread_count_independence(oracle):
     pm, _ = nbtest.gen_random(500, seed=1)
     oracle.set_threads(1); a1 = oracle.forces(pm, PAIRWISE)
