@@ -122,6 +122,8 @@ int nb_timer_stop(nb_ctx* ctx, float* ms);
  *                      | 3 as 2 with 4 i-particles/thread and the near field (adjacent tiles) in FP64 (production)
  *   "j_splits"         0 auto | 1..64 CTAs sharing one i-block's j-range
  *   "spatial_sort"     1 (default) Morton-order the particles at upload | 0 keep the caller's order
+ *   "resort_interval"  re-establish the Morton order from the current positions every so many steps (default 16; 0 never);
+ *                      results stay correct without it, but tiles that lose their compactness take the slower near path
  *   "far_kappa_milli"  1000*kappa of the far-tile criterion box gap > kappa*(half-extent_i + half-extent_j)
  *                      (default 250); 0 = every tile through the near-field path */
 int nb_set_option(nb_ctx* ctx, const char* key, long value);

@@ -93,6 +93,9 @@ size_t sort_temp_bytes(long n);
 int build_permutation(const double4* src_pos, long n, bool spatial, SortScratch& S, unsigned int* perm, cudaStream_t st);
 int launch_gather_state(const double4* src_pos, const double4* src_vel, const unsigned int* perm, long n, long npad,
                         double4* pos, double4* vel, cudaStream_t st);
+int launch_permute4(const double4* src, const unsigned int* p2, long n, double4* dst, cudaStream_t st);
+int launch_permute_acc(const double* acc, long npad, const unsigned int* p2, long n, double* dst, cudaStream_t st);
+int launch_compose_perm(const unsigned int* perm, const unsigned int* p2, long n, unsigned int* dst, cudaStream_t st);
 int launch_scatter4(const double4* src, const unsigned int* perm, long first, long count, double4* dst, cudaStream_t st);
 int launch_scatter_acc(const double* acc, long npad, const unsigned int* perm, long first, long count, double4* dst, cudaStream_t st);
 int launch_snapshot_scatter(const double4* pos, const double4* vel, const unsigned int* perm, long n,

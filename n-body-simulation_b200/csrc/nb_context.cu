@@ -75,6 +75,8 @@ struct nb_ctx {
     double* snap = nullptr;                // snapshot staging [n][6] + [n][2], allocated by the first nb_snapshot
     SortScratch ss;
     int spatial_sort = 1; float kappa = 0.25f;
+    int resort_interval = 16; long steps_since_sort = 0;   // re-establish the Morton order every so many steps
+    unsigned int* perm2 = nullptr;
     double *acc = nullptr, *part = nullptr, *red_part = nullptr, *red = nullptr, *eout = nullptr;
     float* pk = nullptr;
     size_t part_bytes = 0;
@@ -89,11 +91,11 @@ namespace {
 
 void free_arrays(nb_ctx* c) {
     cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->tmp4); cudaFree(c->stage_pos); cudaFree(c->stage_vel);
-    cudaFree(c->acc); cudaFree(c->part); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->perm); cudaFree(c->snap);
+    cudaFree(c->acc); cudaFree(c->part); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->perm); cudaFree(c->perm2); cudaFree(c->snap);
     cudaFree(c->ss.keys_in); cudaFree(c->ss.keys_out); cudaFree(c->ss.idx_in); cudaFree(c->ss.extent_part);
     cudaFree(c->ss.box); cudaFree(c->ss.cub_temp);
     c->pos = c->vel = c->tmp4 = c->stage_pos = c->stage_vel = nullptr;
-    c->acc = c->part = c->red_part = c->snap = nullptr; c->pk = nullptr; c->perm = nullptr; c->part_bytes = 0;
+    c->acc = c->part = c->red_part = c->snap = nullptr; c->pk = nullptr; c->perm = nullptr; c->perm2 = nullptr; c->part_bytes = 0;
     c->ss = SortScratch();
     cudaGetLastError();
 }
@@ -109,6 +111,7 @@ int alloc_arrays(nb_ctx* c) {
     NB_CUDA(cudaMalloc(&c->acc, np * 3 * sizeof(double)));
     NB_CUDA(cudaMalloc(&c->red_part, (np / kThreads) * 4 * sizeof(double)));
     NB_CUDA(cudaMalloc(&c->perm, np * sizeof(unsigned int)));
+    NB_CUDA(cudaMalloc(&c->perm2, np * sizeof(unsigned int)));
     NB_CUDA(cudaMalloc(&c->ss.keys_in, n * sizeof(unsigned long long)));
     NB_CUDA(cudaMalloc(&c->ss.keys_out, n * sizeof(unsigned long long)));
     NB_CUDA(cudaMalloc(&c->ss.idx_in, n * sizeof(unsigned int)));
@@ -244,6 +247,47 @@ int reduce_com(nb_ctx* c) {
     return NB_OK;
 }
 
+// Particles move, so the Morton order established at upload decays and with it the compactness of the tiles (the
+// result stays correct — more tiles simply take the FP64 near path). Every resort_interval steps the order is rebuilt from
+// the current positions: x, v, a and the caller-order permutation are permuted consistently and the tiles re-packed.
+// Multi-GPU: the slices are gathered first, every rank then sorts the identical full state.
+// Multi-GPU: make every rank's copy of the (Morton-ordered) master state complete before it leaves the device.
+int gather_state_all(nb_ctx* c) {
+    if (c->world == 1) return NB_OK;
+    const size_t count = (size_t)c->ni * 4;
+    NB_NCCL(nccl::AllGather((const double*)(c->pos + c->i0), (double*)c->pos, count, nccl::kFloat64, c->comm, c->stream));
+    NB_NCCL(nccl::AllGather((const double*)(c->vel + c->i0), (double*)c->vel, count, nccl::kFloat64, c->comm, c->stream));
+    return NB_OK;
+}
+
+int resort(nb_ctx* c) {
+    if (!c->spatial_sort) return NB_OK;
+    int rc;
+    if (c->world > 1) {
+        NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+        rc = gather_state_all(c); if (rc) return rc;
+        for (int k = 0; k < 3; ++k)
+            NB_NCCL(nccl::AllGather(c->acc + (size_t)k * c->npad + c->i0, c->acc + (size_t)k * c->npad, (size_t)c->ni,
+                                    nccl::kFloat64, c->comm, c->stream));
+    }
+    rc = build_permutation(c->pos, c->n, true, c->ss, c->perm2, c->stream); if (rc) return rc;
+    const size_t nb4 = (size_t)c->n * sizeof(double4);
+    rc = launch_permute4(c->pos, c->perm2, c->n, c->stage_pos, c->stream); if (rc) return rc;
+    NB_CUDA(cudaMemcpyAsync(c->pos, c->stage_pos, nb4, cudaMemcpyDeviceToDevice, c->stream));
+    rc = launch_permute4(c->vel, c->perm2, c->n, c->stage_vel, c->stream); if (rc) return rc;
+    NB_CUDA(cudaMemcpyAsync(c->vel, c->stage_vel, nb4, cudaMemcpyDeviceToDevice, c->stream));
+    double* tmp = reinterpret_cast<double*>(c->tmp4);                       // npad double4 >= 3 npad doubles
+    NB_CUDA(cudaMemcpyAsync(tmp, c->acc, (size_t)c->npad * 3 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+    rc = launch_permute_acc(tmp, c->npad, c->perm2, c->n, c->acc, c->stream); if (rc) return rc;
+    rc = launch_compose_perm(c->perm, c->perm2, c->n, c->ss.idx_in, c->stream); if (rc) return rc;
+    NB_CUDA(cudaMemcpyAsync(c->perm, c->ss.idx_in, (size_t)c->n * sizeof(unsigned int), cudaMemcpyDeviceToDevice, c->stream));
+    StepArrays A = arrays(c);
+    rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream); if (rc) return rc;
+    c->launches += 9;
+    c->steps_since_sort = 0;
+    return NB_OK;
+}
+
 int compute_accel(nb_ctx* c, bool kick, double dt) {
     int S = 0;
     int rc = eval_force(c, &S); if (rc) return rc;
@@ -347,6 +391,7 @@ int nb_set_option(nb_ctx* c, const char* key, long value) {
     if (!strcmp(key, "force_variant")) { if (value < 0 || value > 3) return fail(NB_ERR_INVALID, "force_variant must be 0..3"); c->force_variant = (int)value; return NB_OK; }
     if (!strcmp(key, "j_splits")) { if (value < 0 || value > 64) return fail(NB_ERR_INVALID, "j_splits must be 0..64"); c->j_splits = (int)value; return NB_OK; }
     if (!strcmp(key, "spatial_sort")) { c->spatial_sort = value ? 1 : 0; return NB_OK; }
+    if (!strcmp(key, "resort_interval")) { if (value < 0) return fail(NB_ERR_INVALID, "resort_interval must be >= 0"); c->resort_interval = (int)value; return NB_OK; }
     if (!strcmp(key, "far_kappa_milli")) { if (value < 0) return fail(NB_ERR_INVALID, "far_kappa_milli must be >= 0"); c->kappa = (float)value * 1e-3f; return NB_OK; }
     return fail(NB_ERR_INVALID, "nb_set_option: unknown key '%s'", key);
 }
@@ -396,20 +441,9 @@ int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
     StepArrays A = arrays(c);
     rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream); if (rc) return rc;
     c->launches++;
-    c->uploaded = true; c->have_accel = false;
+    c->uploaded = true; c->have_accel = false; c->steps_since_sort = 0;
     NB_CUDA(cudaStreamSynchronize(c->stream));      // the host buffers may be reused as soon as we return
     return NB_OK;
-}
-
-namespace {
-// Multi-GPU: make every rank's copy of the (Morton-ordered) master state complete before it leaves the device.
-int gather_state_all(nb_ctx* c) {
-    if (c->world == 1) return NB_OK;
-    const size_t count = (size_t)c->ni * 4;
-    NB_NCCL(nccl::AllGather((const double*)(c->pos + c->i0), (double*)c->pos, count, nccl::kFloat64, c->comm, c->stream));
-    NB_NCCL(nccl::AllGather((const double*)(c->vel + c->i0), (double*)c->vel, count, nccl::kFloat64, c->comm, c->stream));
-    return NB_OK;
-}
 }
 
 int nb_download(nb_ctx* c, double* posMass4, double* vel4) {
@@ -462,6 +496,8 @@ int nb_step(nb_ctx* c, double dt, int nsteps) {
     if (!c->have_accel) { rc = nb_compute_accel(c); if (rc) return rc; }
     const bool vv = (c->integ == NB_INTEG_VELOCITY_VERLET);
     for (int s = 0; s < nsteps; ++s) {
+        if (c->resort_interval > 0 && c->steps_since_sort >= c->resort_interval) { rc = resort(c); if (rc) return rc; }
+        c->steps_since_sort++;
         StepArrays A = arrays(c);
         rc = launch_drift(A, c->integ, dt, c->subtract_com != 0, c->avg_mass, c->stream); if (rc) return rc;
         c->launches++;

@@ -137,9 +137,44 @@ snapshot_scatter_kernel(const double4* __restrict__ pos, const double4* __restri
     if (staticData2) { staticData2[o * 2] = (double)o; staticData2[o * 2 + 1] = p.w; }
 }
 
+// re-sort helpers: dst[s] = src[p2[s]] for the first n slots (pads keep their slots)
+__global__ void __launch_bounds__(kThreads)
+permute4_kernel(const double4* __restrict__ src, const unsigned int* __restrict__ p2, long n, double4* __restrict__ dst) {
+    const long s = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (s < n) dst[s] = src[p2[s]];
+}
+__global__ void __launch_bounds__(kThreads)
+permute_acc_kernel(const double* __restrict__ acc, long npad, const unsigned int* __restrict__ p2, long n, double* __restrict__ dst) {
+    const long s = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (s >= n) return;
+    const unsigned int o = p2[s];
+    dst[s] = acc[o]; dst[npad + s] = acc[npad + o]; dst[2 * npad + s] = acc[2 * npad + o];
+}
+__global__ void __launch_bounds__(kThreads)
+compose_perm_kernel(const unsigned int* __restrict__ perm, const unsigned int* __restrict__ p2, long n, unsigned int* __restrict__ dst) {
+    const long s = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (s < n) dst[s] = perm[p2[s]];
+}
+
 inline unsigned blocks_for(long count) { return (unsigned)((count + kThreads - 1) / kThreads); }
 
 } // namespace
+
+int launch_permute4(const double4* src, const unsigned int* p2, long n, double4* dst, cudaStream_t st) {
+    permute4_kernel<<<blocks_for(n), kThreads, 0, st>>>(src, p2, n, dst);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+int launch_permute_acc(const double* acc, long npad, const unsigned int* p2, long n, double* dst, cudaStream_t st) {
+    permute_acc_kernel<<<blocks_for(n), kThreads, 0, st>>>(acc, npad, p2, n, dst);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+int launch_compose_perm(const unsigned int* perm, const unsigned int* p2, long n, unsigned int* dst, cudaStream_t st) {
+    compose_perm_kernel<<<blocks_for(n), kThreads, 0, st>>>(perm, p2, n, dst);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
 
 size_t sort_temp_bytes(long n) {
     size_t bytes = 0;

@@ -33,6 +33,7 @@ tol = 1e-5 if prec == nbtest.FP32 else 1e-12
 with lib.context(n, prec, device=local) as ctx:
     lib.check(lib.l.nb_comm_init(ctx.h, raw, rank, world))
     ctx.set_methods(nbtest.VV, force, 1)
+    ctx.set_option("resort_interval", 2)                  # exercise the collective re-sort inside the 3 steps
     ctx.upload(pm, v)
     ctx.compute_accel()
     a_multi = ctx.accel()

@@ -183,6 +183,29 @@ def test_far_tile_path_and_ordering_options(lib, oracle, gen, force):
     assert err2.max() <= 1.5e-5 and np.quantile(err2, 0.999) <= 3e-6
 
 
+@pytest.mark.parametrize("prec", [FP32, FP64], ids=["fp32", "fp64"])
+def test_periodic_resort_keeps_state_consistent(lib, oracle, prec):
+    """Re-sorting every step permutes x, v, a and the caller-order map consistently: same trajectory as never re-sorting
+    and as the CPU integrator, rows still in the caller's order."""
+    pm, v = nbtest.gen_spiral(5000, seed=14)
+    v[:, :3] *= 40.0                                         # make the particles really move between sorts
+    res = {}
+    for interval in (0, 1, 7):
+        with lib.context(5000, prec) as ctx:
+            ctx.set_option("resort_interval", interval)
+            ctx.set_methods(VV, PAIRWISE, 1)
+            ctx.upload(pm, v)
+            ctx.step(0.02, 30)
+            res[interval] = ctx.download() + (ctx.accel(),)
+    p_ref, v_ref = oracle.step(pm, v, VV, PAIRWISE, 0.02, 30)
+    tol = 2e-5 if prec == FP32 else 1e-9
+    for interval, (p, w, a) in res.items():
+        assert np.array_equal(p[:, 3], pm[:, 3])
+        assert np.abs(p[:, :3] - p_ref[:, :3]).max() <= tol * 3000 and np.abs(w[:, :3] - v_ref[:, :3]).max() <= tol * 3000
+        assert nbtest.rel_err(a, oracle.forces(p, PAIRWISE)).max() <= (1e-5 if prec == FP32 else 1e-9)
+    assert np.abs(res[0][0] - res[1][0]).max() <= tol * 3000
+
+
 def test_run_is_bit_reproducible(lib):
     pm, v = nbtest.gen_spiral(8192, seed=2)
     r1 = lib.run_benchmark(pm, v, VV, PAIRWISE, 0.04, 3, precision=FP32)
