@@ -110,6 +110,10 @@ int nb_last_force_ms(nb_ctx* ctx, float* ms);
 /* Mean duration (ms) of the force evaluations since the last reset (at most the 64 most recent) and how many were
  * averaged; waits for the stream. reset != 0 starts a new measurement window. */
 int nb_force_timing(nb_ctx* ctx, int reset, float* mean_ms, int* evals);
+/* Diagnostics of the production FP32 kernel (after nb_set_option(ctx, "collect_stats", 1), which also resets them):
+ * out[0] j-tiles taken through the CTA-frame far path, out[1] j-tiles refined per warp (both counted once per CTA),
+ * out[2] 64-particle sub-tiles through the warp-frame far path, out[3] sub-tiles evaluated in FP64 (once per warp). */
+int nb_tile_stats(nb_ctx* ctx, unsigned long long out[4]);
 /* CUDA-event stopwatch on the context's stream (torch.cuda.Event only sees torch's own streams):
  * nb_timer_start records the start event; nb_timer_stop records the stop event, waits for it and returns the device
  * time in ms of everything the context enqueued in between. */
@@ -121,7 +125,9 @@ int nb_timer_stop(nb_ctx* ctx, float* ms);
  *                      | 2 bulk-copy (TMA) tiles in the i-block's frame, 2 i-particles/thread, FP32 two-float near field
  *                      | 3 as 2 with 4 i-particles/thread and the near field (adjacent tiles) in FP64 (production)
  *   "j_splits"         0 auto | 1..64 CTAs sharing one i-block's j-range
- *   "spatial_sort"     1 (default) Morton-order the particles at upload | 0 keep the caller's order
+ *   "spatial_sort"     1 (default) order the particles along a 3-D Hilbert curve at upload | 2 Morton (Z) curve
+ *                      | 0 keep the caller's order
+ *   "collect_stats"    1 = count tile classifications (see nb_tile_stats); costs a few atomics per tile
  *   "resort_interval"  re-establish the Morton order from the current positions every so many steps (default 16; 0 never);
  *                      results stay correct without it, but tiles that lose their compactness take the slower near path
  *   "far_kappa_milli"  1000*kappa of the far-tile criterion box gap > kappa*(half-extent_i + half-extent_j)

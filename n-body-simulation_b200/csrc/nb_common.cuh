@@ -26,13 +26,16 @@ constexpr double kR2Cut    = 1e-10;   // core/Forces.cpp:144,350 — pairs with 
 //   row 3     gm         (float)(G * m)
 //   row 4..6  xl yl zl   low parts                   (float)(x - (double)xh)
 //   row 7     mq         (float)(m / (3 * mean mass))   (ADAPTIVE_MUTUAL only)
-//   row 8     meta       [0..2] bbox min, [3..5] bbox max of the tile's hi positions, [6] max |coordinate|; rest unused.
+//   row 8     meta       [0..2] bbox min, [3..5] bbox max of the tile's hi positions, [6] max |coordinate|,
+//                        [8..31] min/max boxes of the four 64-particle sub-tiles; rest unused.
 //                        Travels with the tile (bulk copy, all-gather) so the kernel can pick the cheap path per tile.
 constexpr int kTJ = 256;                 // j-particles per tile == threads per CTA
 //   row 9     gml        (float)(G m - (double)gm): low part of G m for the FP64 near-field path
 constexpr int kNC = 10;                  // rows per tile
 constexpr int kMetaRow = 8;
 constexpr int kGmLoRow = 9;
+constexpr int kSubTile = 64;              // j-particles per sub-tile (classification granularity of near tiles)
+constexpr int kSubBoxOffset = 8;         // meta row: sub-tile boxes start here (4 x 6 floats)
 constexpr int kTileFloats = kTJ * kNC;   // 2560 floats = 10240 bytes
 constexpr int kTileBytes  = kTileFloats * 4;
 constexpr int kAlign = 1024;             // particle counts are padded to a multiple of this (4 tiles)
@@ -45,6 +48,7 @@ struct ForceLaunch {          // one launch = i-tiles [it0, it0+nit) against the
     long npad;                // padded particle count (row stride of `part`)
     int s0, S;                // this launch writes partial slots s0 .. s0+S-1
     float g0;                 // mass scale G * (mean mass) of the mass-scaled far path (> 0)
+    unsigned long long* stats; // optional device counters [4]: far tiles, CTA-near tiles (per CTA), far / FP64 sub-tiles (per warp); or null
     float kappa;              // far-tile criterion: box gap > kappa * (|x|max_i + |x|max_j); huge = always accurate path
 };
 
@@ -56,6 +60,7 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 // nb_force.cu
 int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, int force_method, int variant, cudaStream_t st);
+int launch_force_near64(const float* pk, double* part, const ForceLaunch& L, int force_method, cudaStream_t st);
 int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st);
 int launch_potential_fp64(const double4* pos, double* pot, long npad, int ntiles, cudaStream_t st);
 int force_regs_info(char* buf, int len);
@@ -90,7 +95,7 @@ struct SortScratch {
     void* cub_temp = nullptr; size_t cub_bytes = 0;
 };
 size_t sort_temp_bytes(long n);
-int build_permutation(const double4* src_pos, long n, bool spatial, SortScratch& S, unsigned int* perm, cudaStream_t st);
+int build_permutation(const double4* src_pos, long n, int spatial /* 0 none, 1 Hilbert, 2 Morton */, SortScratch& S, unsigned int* perm, cudaStream_t st);
 int launch_gather_state(const double4* src_pos, const double4* src_vel, const unsigned int* perm, long n, long npad,
                         double4* pos, double4* vel, cudaStream_t st);
 int launch_permute4(const double4* src, const unsigned int* p2, long n, double4* dst, cudaStream_t st);

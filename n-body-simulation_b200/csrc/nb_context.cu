@@ -65,7 +65,8 @@ struct nb_ctx {
     long n = 0, npad = 0; int ntiles = 0;
     int integ = NB_INTEG_VELOCITY_VERLET, force = NB_FORCE_PAIRWISE, subtract_com = 1;
     int rank = 0, world = 1; long i0 = 0, ni = 0;
-    cudaStream_t stream = nullptr, comm_stream = nullptr;
+    cudaStream_t stream = nullptr, comm_stream = nullptr, near_stream = nullptr;
+    cudaEvent_t ev_force_begin = nullptr, ev_near_done = nullptr;
     cudaEvent_t ev_packed = nullptr, ev_gathered = nullptr, tev0 = nullptr, tev1 = nullptr;
     static constexpr int kRing = 64;
     cudaEvent_t fev0[kRing] = {}, fev1[kRing] = {};   // ring of force-evaluation event pairs
@@ -77,6 +78,7 @@ struct nb_ctx {
     int spatial_sort = 1; float kappa = 0.25f;
     int resort_interval = 16; long steps_since_sort = 0;   // re-establish the Morton order every so many steps
     unsigned int* perm2 = nullptr;
+    int collect_stats = 0; unsigned long long* stats = nullptr;   // optional tile-classification counters (device, 4 words)
     double *acc = nullptr, *part = nullptr, *red_part = nullptr, *red = nullptr, *eout = nullptr;
     float* pk = nullptr;
     size_t part_bytes = 0;
@@ -131,7 +133,7 @@ int alloc_arrays(nb_ctx* c) {
 
 // Caller-order device arrays (n rows) -> Morton-ordered, padded master state + packed tiles.
 int ingest(nb_ctx* c, const double4* src_pos, const double4* src_vel) {
-    int rc = build_permutation(src_pos, c->n, c->spatial_sort != 0, c->ss, c->perm, c->stream); if (rc) return rc;
+    int rc = build_permutation(src_pos, c->n, c->spatial_sort, c->ss, c->perm, c->stream); if (rc) return rc;
     rc = launch_gather_state(src_pos, src_vel, c->perm, c->n, c->npad, c->pos, c->vel, c->stream); if (rc) return rc;
     c->launches += 5;
     return NB_OK;
@@ -191,32 +193,55 @@ int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const 
 }
 
 // part[0..S) = partial sums of F(x) for the owned i-slice; returns S. Multi-GPU: the own j-slice is processed while the
-// all-gather of the remote slices is in flight on comm_stream.
+// all-gather of the remote slices is in flight on comm_stream. FP32 production path (variant 3): the FP64 near-field
+// kernel runs on near_stream next to the FP32 far kernel (different pipes) and writes its own partial slots.
 int eval_force(nb_ctx* c, int* S_out) {
-    const int R = c->precision == NB_PREC_FP32 ? force_i_tiles_per_cta(c->force_variant == 0 ? 3 : c->force_variant) : 2;
+    const int variant = c->force_variant == 0 ? 3 : c->force_variant;
+    const bool split_near = (c->precision == NB_PREC_FP32 && variant == 3);
+    const int R = c->precision == NB_PREC_FP32 ? force_i_tiles_per_cta(variant) : 2;
     const int nit = (int)(c->ni / kTJ), it0 = (int)(c->i0 / kTJ);
     const int iblocks = nit / R;
     ForceLaunch L; L.it0 = it0; L.nit = nit; L.ntiles = c->ntiles; L.npad = c->npad;
     L.kappa = c->kappa > 0.f ? c->kappa : 3.0e38f;
     L.g0 = c->avg_mass > 0.0 ? (float)(kG * c->avg_mass) : 1.f;
+    L.stats = c->collect_stats ? c->stats : nullptr;
     const int slot = (int)(c->fev_count % nb_ctx::kRing);
     NB_CUDA(cudaEventRecord(c->fev0[slot], c->stream));
+    int S_far = 0, rc;
+    const int S_near = split_near ? splits_for(c, iblocks, c->ntiles) : 0;
     if (c->world == 1) {
         L.jt0 = 0; L.jcount = c->ntiles; L.s0 = 0; L.S = splits_for(c, iblocks, L.jcount);
-        int rc = ensure_part(c, L.S); if (rc) return rc;
-        rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
-        *S_out = L.S;
+        S_far = L.S;
+        rc = ensure_part(c, S_far + S_near); if (rc) return rc;
     } else {
         const int SA = splits_for(c, iblocks, nit);
         const int SB = splits_for(c, iblocks, c->ntiles - nit);
-        int rc = ensure_part(c, SA + SB); if (rc) return rc;
+        S_far = SA + SB;
+        rc = ensure_part(c, S_far + S_near); if (rc) return rc;
+    }
+    if (split_near) {
+        // near field on its own stream: needs the packed tiles (this stream so far) and, multi-GPU, the gathered slices
+        NB_CUDA(cudaEventRecord(c->ev_force_begin, c->stream));
+        NB_CUDA(cudaStreamWaitEvent(c->near_stream, c->ev_force_begin, 0));
+        if (c->world > 1) NB_CUDA(cudaStreamWaitEvent(c->near_stream, c->ev_gathered, 0));
+        ForceLaunch N = L; N.jt0 = 0; N.jcount = c->ntiles; N.s0 = S_far; N.S = S_near; N.stats = nullptr;
+        rc = launch_force_near64(c->pk, c->part, N, c->force, c->near_stream); if (rc) return rc;
+        c->launches++;
+        NB_CUDA(cudaEventRecord(c->ev_near_done, c->near_stream));
+    }
+    if (c->world == 1) {
+        rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
+    } else {
+        const int SA = splits_for(c, iblocks, nit);
+        const int SB = S_far - SA;
         L.jt0 = it0; L.jcount = nit; L.s0 = 0; L.S = SA;
         rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
         L.jt0 = (it0 + nit) % c->ntiles; L.jcount = c->ntiles - nit; L.s0 = SA; L.S = SB;
         rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
-        *S_out = SA + SB;
     }
+    if (split_near) NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_near_done, 0));
+    *S_out = S_far + S_near;
     NB_CUDA(cudaEventRecord(c->fev1[slot], c->stream));
     c->fev_count++;
     c->force_timed = true;
@@ -270,7 +295,7 @@ int resort(nb_ctx* c) {
             NB_NCCL(nccl::AllGather(c->acc + (size_t)k * c->npad + c->i0, c->acc + (size_t)k * c->npad, (size_t)c->ni,
                                     nccl::kFloat64, c->comm, c->stream));
     }
-    rc = build_permutation(c->pos, c->n, true, c->ss, c->perm2, c->stream); if (rc) return rc;
+    rc = build_permutation(c->pos, c->n, c->spatial_sort, c->ss, c->perm2, c->stream); if (rc) return rc;
     const size_t nb4 = (size_t)c->n * sizeof(double4);
     rc = launch_permute4(c->pos, c->perm2, c->n, c->stage_pos, c->stream); if (rc) return rc;
     NB_CUDA(cudaMemcpyAsync(c->pos, c->stage_pos, nb4, cudaMemcpyDeviceToDevice, c->stream));
@@ -344,6 +369,9 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
 #define NB_TRY(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return bail(cuda_fail(_e, #x, __FILE__, __LINE__)); } while (0)
     NB_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     NB_TRY(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+    NB_TRY(cudaStreamCreateWithFlags(&c->near_stream, cudaStreamNonBlocking));
+    NB_TRY(cudaEventCreateWithFlags(&c->ev_force_begin, cudaEventDisableTiming));
+    NB_TRY(cudaEventCreateWithFlags(&c->ev_near_done, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
     NB_TRY(cudaEventCreate(&c->tev0)); NB_TRY(cudaEventCreate(&c->tev1));
@@ -362,9 +390,10 @@ int nb_destroy(nb_ctx* c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
+    if (c->near_stream) cudaStreamSynchronize(c->near_stream);
     if (c->comm && nccl::CommDestroy) nccl::CommDestroy(c->comm);
     free_arrays(c);
-    cudaFree(c->red); cudaFree(c->eout);
+    cudaFree(c->red); cudaFree(c->eout); cudaFree(c->stats);
     if (c->ev_packed) cudaEventDestroy(c->ev_packed);
     if (c->ev_gathered) cudaEventDestroy(c->ev_gathered);
     if (c->tev0) cudaEventDestroy(c->tev0);
@@ -372,6 +401,9 @@ int nb_destroy(nb_ctx* c) {
     for (int k = 0; k < nb_ctx::kRing; ++k) { if (c->fev0[k]) cudaEventDestroy(c->fev0[k]); if (c->fev1[k]) cudaEventDestroy(c->fev1[k]); }
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
+    if (c->near_stream) cudaStreamDestroy(c->near_stream);
+    if (c->ev_force_begin) cudaEventDestroy(c->ev_force_begin);
+    if (c->ev_near_done) cudaEventDestroy(c->ev_near_done);
     cudaGetLastError();
     delete c;
     return NB_OK;
@@ -390,7 +422,14 @@ int nb_set_option(nb_ctx* c, const char* key, long value) {
     if (!c || !key) return fail(NB_ERR_INVALID, "nb_set_option: NULL argument");
     if (!strcmp(key, "force_variant")) { if (value < 0 || value > 3) return fail(NB_ERR_INVALID, "force_variant must be 0..3"); c->force_variant = (int)value; return NB_OK; }
     if (!strcmp(key, "j_splits")) { if (value < 0 || value > 64) return fail(NB_ERR_INVALID, "j_splits must be 0..64"); c->j_splits = (int)value; return NB_OK; }
-    if (!strcmp(key, "spatial_sort")) { c->spatial_sort = value ? 1 : 0; return NB_OK; }
+    if (!strcmp(key, "spatial_sort")) { if (value < 0 || value > 2) return fail(NB_ERR_INVALID, "spatial_sort must be 0..2"); c->spatial_sort = (int)value; return NB_OK; }
+    if (!strcmp(key, "collect_stats")) {
+        int rc = use_device(c); if (rc) return rc;
+        if (!c->stats) NB_CUDA(cudaMalloc(&c->stats, 4 * sizeof(unsigned long long)));
+        NB_CUDA(cudaMemsetAsync(c->stats, 0, 4 * sizeof(unsigned long long), c->stream));
+        c->collect_stats = value ? 1 : 0;
+        return NB_OK;
+    }
     if (!strcmp(key, "resort_interval")) { if (value < 0) return fail(NB_ERR_INVALID, "resort_interval must be >= 0"); c->resort_interval = (int)value; return NB_OK; }
     if (!strcmp(key, "far_kappa_milli")) { if (value < 0) return fail(NB_ERR_INVALID, "far_kappa_milli must be >= 0"); c->kappa = (float)value * 1e-3f; return NB_OK; }
     return fail(NB_ERR_INVALID, "nb_set_option: unknown key '%s'", key);
@@ -511,6 +550,7 @@ int nb_sync(nb_ctx* c) {
     if (!c) return fail(NB_ERR_INVALID, "nb_sync: ctx is NULL");
     int rc = use_device(c); if (rc) return rc;
     NB_CUDA(cudaStreamSynchronize(c->comm_stream));
+    NB_CUDA(cudaStreamSynchronize(c->near_stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
@@ -596,6 +636,15 @@ int nb_force_timing(nb_ctx* c, int reset, float* mean_ms, int* evals) {
     *mean_ms = cnt ? (float)(sum / (double)cnt) : 0.f;
     *evals = (int)cnt;
     if (reset) c->fev_count = 0;
+    return NB_OK;
+}
+
+int nb_tile_stats(nb_ctx* c, unsigned long long out[4]) {
+    if (!c || !out) return fail(NB_ERR_INVALID, "nb_tile_stats: NULL argument");
+    if (!c->stats) return fail(NB_ERR_INVALID, "nb_tile_stats: enable with nb_set_option(ctx, \"collect_stats\", 1) first");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaMemcpyAsync(out, c->stats, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
 

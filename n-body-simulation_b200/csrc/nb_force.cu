@@ -396,42 +396,48 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
 // ------------------------------------------------------------------------------------------------------------------
 // Variant 3 (production): FP32 far field with FOUR i-particles per thread + FP64 near field.
 //
-// Measured on B200 (tools/pipe_bench, profiles/): a broadcast LDS.128 costs the issuing sub-partition ~4.6 cycles of
-// FMA-pipe time, so with two i-particles per thread (variant 2) the four loads of a j4 group add ~20 % to the 88 pipe
-// cycles of its 8 interactions. Four i-particles per thread halve that. To make room in the register file
-//   * only the far-path state of the i-particles (one float per coordinate, CTA frame) lives in registers,
-//   * the FP64 running sums live in shared memory (touched once per 128 j),
-//   * the near field (the few adjacent tiles) is evaluated one i-tile at a time in FP64, re-deriving the i-particle from
-//     the packed tile. FP64 there is also what keeps the result accurate when two close neighbours pull in opposite
-//     directions (pair terms 100x larger than their sum): those terms are now exact to ~1e-15 instead of ~1e-7.
-// Per j-tile the four i-tiles of the CTA are classified independently (bit r of `mask` = i-tile r is far).
+// * Thread t owns the four CONSECUTIVE particles 4t..4t+3 of the CTA's 1024 (Morton-ordered) i-particles, so a warp
+//   owns 128 consecutive particles: a compact box of its own.
+// * Far field (almost every tile): the CTA-wide frame. While tile q is computed, thread t re-expresses particle t of tile
+//   q+1 relative to the CTA origin O (FP32 for the far loop, FP64 for the near field). One float per coordinate carries
+//   the separation to < 7e-7 as long as the tile's box is further from the CTA's box than kappa (H_cta + h_tile).
+// * Tiles that fail that test (the few tens of tiles around the CTA) are refined per WARP and per SUB-TILE of 64
+//   j-particles: the warp switches its registers to its own frame (origin = centre of its 128 particles), re-expresses the
+//   64 j-particles into a warp-private 1 KB buffer and runs the same far loop — unless the sub-tile's box is within
+//   kappa (H_warp + h_sub) of the warp's box, in which case those 4 x 64 interactions per lane are evaluated in FP64
+//   (two-float positions, two-float G m, branch-free G m s^-3, cut-off and self pairs handled here). Only ~1.5 k of the
+//   N j-particles of an i-particle end up in the FP64 path, independent of N.
+// * FP64 there is also what keeps the result accurate when two close neighbours pull in opposite directions (pair terms
+//   100x larger than their sum): those terms are exact to ~1e-15 instead of ~1e-7.
+// * FP32 partial sums are flushed every 128 j into FP64 sums kept in shared memory (thread-private slots).
 constexpr int kR4 = 4;
-constexpr int kFarFloats = 4 * kTJ;                         // rows k x', k y', k z', k  (PAIRWISE)  |  x', y', z', -  (ADAPTIVE_MUTUAL)
-constexpr int kXfFloats = kFarFloats + 3 * kTJ * 2;         // + three rows of doubles (x', y', z') for the FP64 near path
-constexpr size_t kR4SmemBytes = (size_t)kStages * kTileBytes + 2 * (size_t)kXfFloats * 4 + (size_t)kR4 * 3 * kTJ * 8 + 32 + kStages * 8;
+constexpr int kFarFloats = 4 * kTJ;                         // rows k x', k y', k z', k  (PAIRWISE/PLUMMER)  |  x', y', z', -  (ADAPTIVE)
+constexpr int kXfFloats = kFarFloats;
+constexpr int kWarpXfFloats = 4 * kSubTile;                 // warp-private re-expressed sub-tile (same four rows)
+constexpr size_t kR4SmemBytes = (size_t)kStages * kTileBytes + 2 * (size_t)kXfFloats * 4 + (size_t)kR4 * 3 * kTJ * 8 +
+                                (size_t)(kThreads / 32) * kWarpXfFloats * 4 + kStages * 8 + 8;
 
 template <int MODE>
 struct IState4 {
-    float2 nx[kR4], ny[kR4], nz[kR4];   // -(x'_i) duplicated in both halves (CTA frame)
+    float2 nx[kR4], ny[kR4], nz[kR4];   // -(x'_i) duplicated in both halves (current frame)
     float2 mq[kR4];                     // m_i / (3 mean mass) (ADAPTIVE_MUTUAL)
     float2 ax[kR4], ay[kR4], az[kR4];   // FP32 partial sums
 };
 
-// far field: the four i-particles of the thread against one j4 group.
-//   PAIRWISE: mass-scaled frame — the tile holds k_j x'_j and k_j with k_j = sqrt(G0 / (G m_j)); d' = k_j (x'_j - x'_i) is
-//   one FFMA2 per coordinate and (G m_j / G0) d / r^3 = d' / |d'|^3, so the multiplication by G m_j disappears
-//   (11 packed operations per pair; measured 3 % faster than the 12-operation form in this kernel).
-//   ADAPTIVE: plain frame, G m_j and m_j/(3 mbar) from the raw tile.
-//   MASKED: i-tiles whose bit in `mask` is clear are in the near field of this j-tile and are handled in FP64
-//   elsewhere; their contribution is switched off here (the select also removes the inf of a self pair).
-template <int MODE, bool MASKED>
-__device__ __forceinline__ void far_j4(IState4<MODE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
-                                       int j4, uint32_t mask) {
-    const float4 X = reinterpret_cast<const float4*>(Tf + 0 * kTJ)[j4];
-    const float4 Y = reinterpret_cast<const float4*>(Tf + 1 * kTJ)[j4];
-    const float4 Z = reinterpret_cast<const float4*>(Tf + 2 * kTJ)[j4];
+// far field: the four i-particles of the thread against one j4 group. Tf: re-expressed rows with stride STRIDE,
+// raw: rows of the raw tile (stride kTJ) already offset to the first j of Tf.
+//   PAIRWISE / PLUMMER: mass-scaled frame — Tf holds k_j x'_j and k_j = sqrt(G0 / (G m_j)); d' = k_j (x'_j - x'_i) is one
+//   FFMA2 per coordinate and (G m_j / G0) d / r^3 = d' / |d'|^3, so the multiplication by G m_j disappears
+//   (11 packed operations per pair). ADAPTIVE: plain frame, G m_j and m_j/(3 mbar) from the raw tile.
+// The cost of a packed instruction is set by register-file bandwidth as much as by the FMA pipe: with three distinct
+// 64-bit sources (the accumulating FFMA2s) it takes 3 cycles, not 2 (tools/sass_rf_model.py).
+template <int MODE, int STRIDE>
+__device__ __forceinline__ void far_j4(IState4<MODE>& S, const float* __restrict__ Tf, const float* __restrict__ raw, int j4) {
+    const float4 X = reinterpret_cast<const float4*>(Tf + 0 * STRIDE)[j4];
+    const float4 Y = reinterpret_cast<const float4*>(Tf + 1 * STRIDE)[j4];
+    const float4 Z = reinterpret_cast<const float4*>(Tf + 2 * STRIDE)[j4];
     const float4 K = IS_ADAPTIVE(MODE) ? reinterpret_cast<const float4*>(raw + 3 * kTJ)[j4]       // G m_j
-                              : reinterpret_cast<const float4*>(Tf + 3 * kTJ)[j4];       // k_j
+                                       : reinterpret_cast<const float4*>(Tf + 3 * STRIDE)[j4];    // k_j
     float4 MQ = make_float4(0.f, 0.f, 0.f, 0.f);
     if (IS_ADAPTIVE(MODE)) MQ = reinterpret_cast<const float4*>(raw + 7 * kTJ)[j4];
 #pragma unroll
@@ -464,10 +470,6 @@ __device__ __forceinline__ void far_j4(IState4<MODE>& S, const float* __restrict
                 s2.x = fmaxf(sa.x, sb.x); s2.y = fmaxf(sa.y, sb.y);
             }
             float2 ri; ri.x = rsq_approx(s2.x); ri.y = rsq_approx(s2.y);
-            if (MASKED) {
-                const bool on = (mask >> r) & 1u;
-                ri.x = on ? ri.x : 0.f; ri.y = on ? ri.y : 0.f;
-            }
             const float2 ri2 = __fmul2_rn(ri, ri);
             float2 sc;
             if (!IS_ADAPTIVE(MODE)) sc = __fmul2_rn(ri, ri2);
@@ -477,58 +479,91 @@ __device__ __forceinline__ void far_j4(IState4<MODE>& S, const float* __restrict
     }
 }
 
-// whole tile, far field; FP32 partial sums are flushed into the FP64 sums in shared memory (thread-private slots)
-// every 128 j. PAIRWISE sums are in units of G0 (mass-scaled frame).
-template <int MODE, bool MASKED>
-__device__ __forceinline__ void far_tile(IState4<MODE>& S, const float* __restrict__ Tf, const float* __restrict__ raw,
-                                         double* __restrict__ dacc, int t, float g0, uint32_t mask) {
-    const float unit = IS_ADAPTIVE(MODE) ? 1.f : g0;
-#pragma unroll 1
-    for (int half = 0; half < 2; ++half) {
-#pragma unroll 2
-        for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4) far_j4<MODE, MASKED>(S, Tf, raw, j4, mask);
-#pragma unroll
-        for (int r = 0; r < kR4; ++r) {
-            double* d = dacc + (size_t)r * 3 * kTJ + t;
-            d[0] += (double)((S.ax[r].x + S.ax[r].y) * unit);
-            d[kTJ] += (double)((S.ay[r].x + S.ay[r].y) * unit);
-            d[2 * kTJ] += (double)((S.az[r].x + S.az[r].y) * unit);
-            S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
-        }
-    }
-}
-
-// whole tile, FP64 near field, ONE i-particle (i-tile `itile`, lane t), CTA frame origin O
+// FP32 partial sums -> FP64 sums in shared memory. PAIRWISE / PLUMMER sums are in units of G0 (mass-scaled frame).
 template <int MODE>
-__device__ __forceinline__ void near_tile64(const float* __restrict__ pk, int itile, int t, const float* __restrict__ O,
-                                            const double* __restrict__ Td, const float* __restrict__ raw,
-                                            double* __restrict__ d3 /* dacc + r*3*kTJ + t */) {
-    const float* p = pk + (size_t)itile * kTileFloats + t;
-    const double xi = ((double)p[0 * kTJ] - (double)O[0]) + (double)p[4 * kTJ];
-    const double yi = ((double)p[1 * kTJ] - (double)O[1]) + (double)p[5 * kTJ];
-    const double zi = ((double)p[2 * kTJ] - (double)O[2]) + (double)p[6 * kTJ];
-    const double mqi = IS_ADAPTIVE(MODE) ? (double)p[7 * kTJ] : 0.0;
-    double ax = 0.0, ay = 0.0, az = 0.0;
-#pragma unroll 4
-    for (int j = 0; j < kTJ; ++j) {
-        const double dx = Td[j] - xi, dy = Td[kTJ + j] - yi, dz = Td[2 * kTJ + j] - zi;
-        const double gm = (double)raw[3 * kTJ + j] + (double)raw[kGmLoRow * kTJ + j];
-        const double r2 = dx * dx + dy * dy + dz * dz;
-        double s2 = r2;
-        if (IS_ADAPTIVE(MODE)) {
-            const double w = pow23(mqi + (double)raw[7 * kTJ + j]);
-            s2 = fmax(fma(r2 * w, 1e-4, r2), r2 + 1e-8);
-        }
-        if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
-        double sc = gm_inv_r3(s2, gm);
-        if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off and self pair
-        ax = fma(sc, dx, ax); ay = fma(sc, dy, ay); az = fma(sc, dz, az);
+__device__ __forceinline__ void flush4(IState4<MODE>& S, double* __restrict__ dacc, int t, float g0) {
+    const float unit = IS_ADAPTIVE(MODE) ? 1.f : g0;
+#pragma unroll
+    for (int r = 0; r < kR4; ++r) {
+        double* d = dacc + (size_t)r * 3 * kTJ + t;
+        d[0] += (double)((S.ax[r].x + S.ax[r].y) * unit);
+        d[kTJ] += (double)((S.ay[r].x + S.ay[r].y) * unit);
+        d[2 * kTJ] += (double)((S.az[r].x + S.az[r].y) * unit);
+        S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
     }
-    d3[0] += ax; d3[kTJ] += ay; d3[2 * kTJ] += az;
 }
 
-// per-i-tile bounding boxes of the CTA: thread r (< kR4) owns box r and classifies the j-tiles for it
-struct IBox1 { float lo[3], hi[3]; };
+struct Box3 { float lo[3], hi[3]; };
+// Squared gap between box a and box (blo, bhi), and the half-extent hb of the latter. Used by BOTH the far kernel and the
+// FP64 near kernel to decide which of them owns a (warp, sub-tile) pair, so every operation is pinned (no contraction
+// freedom): the two kernels must reach bit-identical decisions.
+__device__ __forceinline__ float box_gap2(const Box3& a, const float* __restrict__ blo, const float* __restrict__ bhi, float& hb) {
+    float g2 = 0.f; hb = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const float g = fmaxf(0.f, fmaxf(__fsub_rn(blo[c], a.hi[c]), __fsub_rn(a.lo[c], bhi[c])));
+        g2 = __fmaf_rn(g, g, g2);
+        hb = fmaxf(hb, __fmul_rn(0.5f, __fsub_rn(bhi[c], blo[c])));
+    }
+    return g2;
+}
+// true: the pair of boxes is handled by the FP32 far path; false: refine / FP64
+__device__ __forceinline__ bool boxes_far(const Box3& a, float half_a, const float* __restrict__ blo, const float* __restrict__ bhi,
+                                          float kappa, float min_gap2) {
+    float hb;
+    const float g2 = box_gap2(a, blo, bhi, hb);
+    const float thr = __fmul_rn(kappa, __fadd_rn(half_a, hb));
+    return (g2 > __fmul_rn(thr, thr)) && (g2 > min_gap2);
+}
+// union box of the kR4 i-tiles of a CTA and its half-extent (from the tiles' meta rows)
+__device__ __forceinline__ void cta_box(Box3& B, float& half, float* O, const float* __restrict__ pk, int itile_first, int ntile) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) { B.lo[c] = 3.0e38f; B.hi[c] = -3.0e38f; }
+    for (int r = 0; r < ntile; ++r) {
+        const float* m = pk + (size_t)(itile_first + r) * kTileFloats + kMetaRow * kTJ;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) { B.lo[c] = fminf(B.lo[c], __ldg(m + c)); B.hi[c] = fmaxf(B.hi[c], __ldg(m + 3 + c)); }
+    }
+    half = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        O[c] = __fadd_rn(__fmul_rn(0.5f, B.lo[c]), __fmul_rn(0.5f, B.hi[c]));
+        half = fmaxf(half, __fmul_rn(0.5f, __fsub_rn(B.hi[c], B.lo[c])));
+    }
+}
+// box / centre / half-extent of the 128 consecutive particles a warp owns (lane: 4 particles, hi parts)
+__device__ __forceinline__ void warp_box(Box3& W, float* Ow, float& Hw, const float* __restrict__ ip) {
+    const float4 xh = *reinterpret_cast<const float4*>(ip + 0 * kTJ), yh = *reinterpret_cast<const float4*>(ip + 1 * kTJ),
+                 zh = *reinterpret_cast<const float4*>(ip + 2 * kTJ);
+    W.lo[0] = fminf(fminf(xh.x, xh.y), fminf(xh.z, xh.w)); W.hi[0] = fmaxf(fmaxf(xh.x, xh.y), fmaxf(xh.z, xh.w));
+    W.lo[1] = fminf(fminf(yh.x, yh.y), fminf(yh.z, yh.w)); W.hi[1] = fmaxf(fmaxf(yh.x, yh.y), fmaxf(yh.z, yh.w));
+    W.lo[2] = fminf(fminf(zh.x, zh.y), fminf(zh.z, zh.w)); W.hi[2] = fmaxf(fmaxf(zh.x, zh.y), fmaxf(zh.z, zh.w));
+    Hw = 0.f;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            W.lo[c] = fminf(W.lo[c], __shfl_xor_sync(0xffffffffu, W.lo[c], o));
+            W.hi[c] = fmaxf(W.hi[c], __shfl_xor_sync(0xffffffffu, W.hi[c], o));
+        }
+        Ow[c] = __fadd_rn(__fmul_rn(0.5f, W.lo[c]), __fmul_rn(0.5f, W.hi[c]));
+        Hw = fmaxf(Hw, __fmul_rn(0.5f, __fsub_rn(W.hi[c], W.lo[c])));
+    }
+}
+
+// the thread's four particles in the frame with origin O: registers S.nx/ny/nz
+template <int MODE>
+__device__ __forceinline__ void load_i_frame(IState4<MODE>& S, const float* __restrict__ ip /* tile row 0 at the thread's first particle */,
+                                             const float* __restrict__ O) {
+    const float4 xh = *reinterpret_cast<const float4*>(ip + 0 * kTJ), xl = *reinterpret_cast<const float4*>(ip + 4 * kTJ);
+    const float4 yh = *reinterpret_cast<const float4*>(ip + 1 * kTJ), yl = *reinterpret_cast<const float4*>(ip + 5 * kTJ);
+    const float4 zh = *reinterpret_cast<const float4*>(ip + 2 * kTJ), zl = *reinterpret_cast<const float4*>(ip + 6 * kTJ);
+    const float xs[4] = {-((xh.x - O[0]) + xl.x), -((xh.y - O[0]) + xl.y), -((xh.z - O[0]) + xl.z), -((xh.w - O[0]) + xl.w)};
+    const float ys[4] = {-((yh.x - O[1]) + yl.x), -((yh.y - O[1]) + yl.y), -((yh.z - O[1]) + yl.z), -((yh.w - O[1]) + yl.w)};
+    const float zs[4] = {-((zh.x - O[2]) + zl.x), -((zh.y - O[2]) + zl.y), -((zh.z - O[2]) + zl.z), -((zh.w - O[2]) + zl.w)};
+#pragma unroll
+    for (int r = 0; r < kR4; ++r) { S.nx[r] = make_float2(xs[r], xs[r]); S.ny[r] = make_float2(ys[r], ys[r]); S.nz[r] = make_float2(zs[r], zs[r]); }
+}
 
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
@@ -537,9 +572,9 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
     float* raw = reinterpret_cast<float*>(smem_raw);                                        // [kStages][kTileFloats]
     float* T = raw + kStages * kTileFloats;                                                 // [2][kXfFloats]
     double* dacc = reinterpret_cast<double*>(T + 2 * kXfFloats);                            // [kR4*3][kTJ]
-    uint32_t* flags = reinterpret_cast<uint32_t*>(dacc + kR4 * 3 * kTJ);                    // [2][4] far flag of i-tile r, by tile parity
-    uint64_t* full = reinterpret_cast<uint64_t*>(flags + 8);                                // [kStages]
-    const int t = threadIdx.x, s = blockIdx.y;
+    float* Tw = reinterpret_cast<float*>(dacc + kR4 * 3 * kTJ) + (threadIdx.x >> 5) * kWarpXfFloats;   // warp-private [4][kSubTile]
+    uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<float*>(dacc + kR4 * 3 * kTJ) + (kThreads / 32) * kWarpXfFloats);
+    const int t = threadIdx.x, lane = t & 31, s = blockIdx.y;
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
     const int cnt = k1 - k0;
     const int itile_first = L.it0 + blockIdx.x * kR4;
@@ -558,87 +593,186 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
             bulk_g2s(raw + q * kTileFloats, pk + (size_t)wrap_tile(L.jt0 + k0 + q, L.ntiles) * kTileFloats, kTileBytes, &full[q]);
         }
     }
-    CtaFrame F;
-    load_frame<kR4>(F, pk, itile_first);
-    IBox1 B;                                   // box of i-tile min(t, 3); only threads 0..3 use it
-    {
-        const float* m = pk + (size_t)(itile_first + (t < kR4 ? t : kR4 - 1)) * kTileFloats + kMetaRow * kTJ;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) { B.lo[c] = __ldg(m + c); B.hi[c] = __ldg(m + 3 + c); }
-    }
+    CtaFrame F;                                // CTA-wide frame: union box of the four i-tiles
+    Box3 Fbox;
+    cta_box(Fbox, F.half, F.O, pk, itile_first, kR4);
+    // the thread's four consecutive particles: tile itile_first + t/64, offset 4 (t % 64)
+    const size_t i_first = (size_t)itile_first * kTJ + 4 * (size_t)t;
+    const float* ip = pk + (i_first / kTJ) * kTileFloats + (i_first % kTJ);
+    const float min_gap2 = IS_PLUMMER(MODE) ? 1e-2f : 1e-8f;
     const float inv_g0 = 1.f / L.g0;
     IState4<MODE> S;
-#pragma unroll
-    for (int r = 0; r < kR4; ++r) {
-        const float* p = pk + (size_t)(itile_first + r) * kTileFloats + t;
-        float v;
-        v = -((p[0 * kTJ] - F.O[0]) + p[4 * kTJ]); S.nx[r] = make_float2(v, v);
-        v = -((p[1 * kTJ] - F.O[1]) + p[5 * kTJ]); S.ny[r] = make_float2(v, v);
-        v = -((p[2 * kTJ] - F.O[2]) + p[6 * kTJ]); S.nz[r] = make_float2(v, v);
-        v = IS_ADAPTIVE(MODE) ? p[7 * kTJ] : 0.f; S.mq[r] = make_float2(v, v);
-        S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
+    load_i_frame<MODE>(S, ip, F.O);
+    {
+        const float4 m4 = IS_ADAPTIVE(MODE) ? *reinterpret_cast<const float4*>(ip + 7 * kTJ) : make_float4(0.f, 0.f, 0.f, 0.f);
+        S.mq[0] = make_float2(m4.x, m4.x); S.mq[1] = make_float2(m4.y, m4.y); S.mq[2] = make_float2(m4.z, m4.z); S.mq[3] = make_float2(m4.w, m4.w);
     }
-    // classify (thread r < 4) and re-express (thread t <-> particle t) tile q into buffer q & 1
+#pragma unroll
+    for (int r = 0; r < kR4; ++r) S.ax[r] = S.ay[r] = S.az[r] = make_float2(0.f, 0.f);
+    // the warp's own box and frame (128 consecutive particles)
+    Box3 Wbox; float Ow[3], Hw;
+    warp_box(Wbox, Ow, Hw, ip);
+    // re-express (thread t <-> particle t) tile q into buffer q & 1: FP32 rows in the CTA frame
     auto prepare = [&](int q) {
         const float* rw = raw + (q % kStages) * kTileFloats;
         float* Tf = T + (q & 1) * kXfFloats;
-        double* Td = reinterpret_cast<double*>(Tf + kFarFloats);
-        const float* meta = rw + kMetaRow * kTJ;
-        if (t < kR4) {
-            float g2 = 0.f, hj = 0.f;
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                const float g = fmaxf(0.f, fmaxf(meta[c] - B.hi[c], B.lo[c] - meta[3 + c]));
-                g2 = fmaf(g, g, g2);
-                hj = fmaxf(hj, 0.5f * (meta[3 + c] - meta[c]));
-            }
-            const float thr = L.kappa * (F.half + hj);          // F.half: half-extent of the whole i-block (frame size)
-            flags[(q & 1) * 4 + t] = ((g2 > thr * thr) && (g2 > (IS_PLUMMER(MODE) ? 1e-2f : 1e-8f))) ? 1u : 0u;
-        }
-        float kj = 1.f;     // PAIRWISE: k_j = sqrt(G0 / (G m_j)); massless particles get a huge finite k, their r'^2 overflows
-                            // to +inf, rsqrt gives 0 and they contribute exactly nothing
+        float kj = 1.f;     // k_j = sqrt(G0 / (G m_j)); massless particles get a huge finite k, their r'^2 overflows to +inf,
+                            // rsqrt gives 0 and they contribute exactly nothing
         if (!IS_ADAPTIVE(MODE)) { kj = rsq_approx(fmaxf(rw[3 * kTJ + t] * inv_g0, 1e-30f)); Tf[3 * kTJ + t] = kj; }
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
             const float xh = rw[c * kTJ + t], xl = rw[(4 + c) * kTJ + t];
             Tf[c * kTJ + t] = ((xh - F.O[c]) + xl) * kj;
-            Td[c * kTJ + t] = ((double)xh - (double)F.O[c]) + (double)xl;
         }
     };
     if (cnt > 0) { mbar_wait(&full[0], 0u); prepare(0); }
     __syncthreads();
     for (int q = 0; q < cnt; ++q) {
         const int b = q % kStages;
-        if (q + 1 < cnt) {                     // classify + re-express the next tile while this one is being computed
+        if (q + 1 < cnt) {                     // re-express the next tile while this one is being computed
             mbar_wait(&full[(q + 1) % kStages], (uint32_t)(((q + 1) / kStages) & 1));
             prepare(q + 1);
         }
-        const uint4 fl = *reinterpret_cast<const uint4*>(flags + (q & 1) * 4);
-        const uint32_t mask = fl.x | (fl.y << 1) | (fl.z << 2) | (fl.w << 3);
         const float* rw = raw + b * kTileFloats;
+        const float* meta = rw + kMetaRow * kTJ;
         const float* Tf = T + (q & 1) * kXfFloats;
-        const double* Td = reinterpret_cast<const double*>(Tf + kFarFloats);
-        if (mask == 0xFu) {
-            far_tile<MODE, false>(S, Tf, rw, dacc, t, L.g0, mask);
-        } else {
-            if (mask != 0u) far_tile<MODE, true>(S, Tf, rw, dacc, t, L.g0, mask);
+        const bool far_cta = boxes_far(Fbox, F.half, meta, meta + 3, L.kappa, min_gap2);
+        if (L.stats && t == 0) atomicAdd(L.stats + (far_cta ? 0 : 1), 1ULL);
+        if (far_cta) {
+            // ---- far tile: CTA frame, 64 j4 groups
 #pragma unroll 1
-            for (int r = 0; r < kR4; ++r)
-                if (!((mask >> r) & 1u)) near_tile64<MODE>(pk, itile_first + r, t, F.O, Td, rw, dacc + (size_t)r * 3 * kTJ + t);
+            for (int half = 0; half < 2; ++half) {
+#pragma unroll 2
+                for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4) far_j4<MODE, kTJ>(S, Tf, rw, j4);
+                flush4<MODE>(S, dacc, t, L.g0);
+            }
+        } else {
+            // ---- tile close to the CTA: per warp, per sub-tile, in the warp's own frame
+            load_i_frame<MODE>(S, ip, Ow);
+#pragma unroll 1
+            for (int sb = 0; sb < kTJ / kSubTile; ++sb) {
+                const float* sbox = meta + kSubBoxOffset + 6 * sb;
+                const bool far_w = boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2);
+                const int j0 = sb * kSubTile;
+                if (L.stats && lane == 0) atomicAdd(L.stats + (far_w ? 2 : 3), 1ULL);
+                if (far_w) {
+                    __syncwarp();
+#pragma unroll
+                    for (int k = lane; k < kSubTile; k += 32) {          // two particles per lane
+                        const int j = j0 + k;
+                        float kj = 1.f;
+                        if (!IS_ADAPTIVE(MODE)) { kj = rsq_approx(fmaxf(rw[3 * kTJ + j] * inv_g0, 1e-30f)); Tw[3 * kSubTile + k] = kj; }
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) Tw[c * kSubTile + k] = ((rw[c * kTJ + j] - Ow[c]) + rw[(4 + c) * kTJ + j]) * kj;
+                    }
+                    __syncwarp();
+#pragma unroll 2
+                    for (int j4 = 0; j4 < kSubTile / 4; ++j4) far_j4<MODE, kSubTile>(S, Tw, rw + j0, j4);
+                }   // else: this (warp, sub-tile) pair belongs to force_near64_kernel
+            }
+            flush4<MODE>(S, dacc, t, L.g0);
+            load_i_frame<MODE>(S, ip, F.O);
         }
-        __syncthreads();                       // all warps done with raw[b], T[q&1], flags[q&1]; tile q+1 is prepared
+        __syncthreads();                       // all warps done with raw[b] and T[q&1]; tile q+1 is prepared
         if (t == 0 && q + kStages < cnt) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             mbar_expect_tx(&full[b], kTileBytes);
             bulk_g2s(raw + b * kTileFloats, pk + (size_t)wrap_tile(L.jt0 + k0 + q + kStages, L.ntiles) * kTileFloats, kTileBytes, &full[b]);
         }
     }
-    double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad;
+    double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad + i_first;
 #pragma unroll
-    for (int r = 0; r < kR4; ++r) {
-        const size_t i = (size_t)(itile_first + r) * kTJ + t;
-        o[i] = dacc[(r * 3 + 0) * kTJ + t]; o[(size_t)L.npad + i] = dacc[(r * 3 + 1) * kTJ + t]; o[2 * (size_t)L.npad + i] = dacc[(r * 3 + 2) * kTJ + t];
+    for (int c = 0; c < 3; ++c) {
+        double4 v;
+        v.x = dacc[(0 * 3 + c) * kTJ + t]; v.y = dacc[(1 * 3 + c) * kTJ + t]; v.z = dacc[(2 * 3 + c) * kTJ + t]; v.w = dacc[(3 * 3 + c) * kTJ + t];
+        *reinterpret_cast<double4*>(o + (size_t)c * L.npad) = v;
     }
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// FP64 near field of the production path: every (warp of 128 i-particles, sub-tile of 64 j-particles) pair that the far
+// kernel classifies as too close for FP32 (same pinned box tests, bit-identical decisions) is evaluated here in double
+// on the two-float positions and two-float G m: self pairs, pairs under the cut-off and all close encounters live here.
+// Warps are independent (no CTA barrier): a warp walks the meta rows of its j-range, skips what the far kernel takes and
+// stages the rare near sub-tile into a warp-private 2 KB buffer. ~0.3 % (N = 1M) to ~4 % (N = 65 536) of all pairs;
+// the kernel runs on its own stream next to the far kernel — the FP64 pipe is idle there.
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 2)
+force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
+    __shared__ __align__(16) double Jw[kThreads / 32][4][kSubTile];      // x', y', z' (warp frame), G m
+    __shared__ float Mq[kThreads / 32][kSubTile];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5, s = blockIdx.y;
+    const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
+    const int itile_first = L.it0 + blockIdx.x * kR4;
+    Box3 Fbox; float Fhalf, FO[3];
+    cta_box(Fbox, Fhalf, FO, pk, itile_first, kR4);
+    const size_t i_first = (size_t)itile_first * kTJ + 4 * (size_t)t;
+    const float* ip = pk + (i_first / kTJ) * kTileFloats + (i_first % kTJ);
+    Box3 Wbox; float Ow[3], Hw;
+    warp_box(Wbox, Ow, Hw, ip);
+    const float min_gap2 = IS_PLUMMER(MODE) ? 1e-2f : 1e-8f;
+    double xi[kR4], yi[kR4], zi[kR4], mqi[kR4], ax[kR4], ay[kR4], az[kR4];
+    {
+        const float4 xh = *reinterpret_cast<const float4*>(ip + 0 * kTJ), xl = *reinterpret_cast<const float4*>(ip + 4 * kTJ);
+        const float4 yh = *reinterpret_cast<const float4*>(ip + 1 * kTJ), yl = *reinterpret_cast<const float4*>(ip + 5 * kTJ);
+        const float4 zh = *reinterpret_cast<const float4*>(ip + 2 * kTJ), zl = *reinterpret_cast<const float4*>(ip + 6 * kTJ);
+        const float4 mq = *reinterpret_cast<const float4*>(ip + 7 * kTJ);
+        const float h[3][4] = {{xh.x, xh.y, xh.z, xh.w}, {yh.x, yh.y, yh.z, yh.w}, {zh.x, zh.y, zh.z, zh.w}};
+        const float l[3][4] = {{xl.x, xl.y, xl.z, xl.w}, {yl.x, yl.y, yl.z, yl.w}, {zl.x, zl.y, zl.z, zl.w}};
+        const float m[4] = {mq.x, mq.y, mq.z, mq.w};
+#pragma unroll
+        for (int r = 0; r < kR4; ++r) {
+            xi[r] = ((double)h[0][r] - (double)Ow[0]) + (double)l[0][r];
+            yi[r] = ((double)h[1][r] - (double)Ow[1]) + (double)l[1][r];
+            zi[r] = ((double)h[2][r] - (double)Ow[2]) + (double)l[2][r];
+            mqi[r] = (double)m[r];
+            ax[r] = ay[r] = az[r] = 0.0;
+        }
+    }
+    for (int k = k0; k < k1; ++k) {
+        const float* tile = pk + (size_t)wrap_tile(L.jt0 + k, L.ntiles) * kTileFloats;
+        const float* meta = tile + kMetaRow * kTJ;
+        if (boxes_far(Fbox, Fhalf, meta, meta + 3, L.kappa, min_gap2)) continue;       // whole tile: far kernel, CTA frame
+#pragma unroll 1
+        for (int sb = 0; sb < kTJ / kSubTile; ++sb) {
+            const float* sbox = meta + kSubBoxOffset + 6 * sb;
+            if (boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) continue;      // far kernel, warp frame
+            __syncwarp();
+#pragma unroll
+            for (int q = lane; q < kSubTile; q += 32) {
+                const float* pj = tile + sb * kSubTile + q;
+                Jw[w][0][q] = ((double)pj[0 * kTJ] - (double)Ow[0]) + (double)pj[4 * kTJ];
+                Jw[w][1][q] = ((double)pj[1 * kTJ] - (double)Ow[1]) + (double)pj[5 * kTJ];
+                Jw[w][2][q] = ((double)pj[2 * kTJ] - (double)Ow[2]) + (double)pj[6 * kTJ];
+                Jw[w][3][q] = (double)pj[3 * kTJ] + (double)pj[kGmLoRow * kTJ];
+                if (IS_ADAPTIVE(MODE)) Mq[w][q] = pj[7 * kTJ];
+            }
+            __syncwarp();
+#pragma unroll 2
+            for (int j = 0; j < kSubTile; ++j) {
+                const double xj = Jw[w][0][j], yj = Jw[w][1][j], zj = Jw[w][2][j], gm = Jw[w][3][j];
+                const double mqj = IS_ADAPTIVE(MODE) ? (double)Mq[w][j] : 0.0;
+#pragma unroll
+                for (int r = 0; r < kR4; ++r) {
+                    const double dx = xj - xi[r], dy = yj - yi[r], dz = zj - zi[r];
+                    const double r2 = dx * dx + dy * dy + dz * dz;
+                    double s2 = r2;
+                    if (IS_ADAPTIVE(MODE)) {
+                        const double wq = pow23(mqi[r] + mqj);
+                        s2 = fmax(fma(r2 * wq, 1e-4, r2), r2 + 1e-8);
+                    }
+                    if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
+                    double sc = gm_inv_r3(s2, gm);
+                    if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
+                    ax[r] = fma(sc, dx, ax[r]); ay[r] = fma(sc, dy, ay[r]); az[r] = fma(sc, dz, az[r]);
+                }
+            }
+        }
+    }
+    double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad + i_first;
+    *reinterpret_cast<double4*>(o) = make_double4(ax[0], ax[1], ax[2], ax[3]);
+    *reinterpret_cast<double4*>(o + (size_t)L.npad) = make_double4(ay[0], ay[1], ay[2], ay[3]);
+    *reinterpret_cast<double4*>(o + 2 * (size_t)L.npad) = make_double4(az[0], az[1], az[2], az[3]);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -767,6 +901,21 @@ int launch_fp32_mode(const float* pk, double* part, const ForceLaunch& L, int va
         dim3 grid(L.nit / kR32, L.S), block(kThreads);
         if (variant == 2) force_fp32_tma_kernel<kR32, MODE><<<grid, block, 0, st>>>(pk, part, L);
         else              force_fp32_ld_kernel<kR32, MODE><<<grid, block, 0, st>>>(pk, part, L);
+    }
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
+// FP64 near field of variant 3 (same grid decomposition and ForceLaunch as the far kernel, its own partial slots L.s0..)
+int launch_force_near64(const float* pk, double* part, const ForceLaunch& L, int force_method, cudaStream_t st) {
+    if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
+    if (L.nit % kR4 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR4);
+    dim3 grid(L.nit / kR4, L.S), block(kThreads);
+    switch (force_method) {
+        case kPairwise: force_near64_kernel<kPairwise><<<grid, block, 0, st>>>(pk, part, L); break;
+        case kPlummer:  force_near64_kernel<kPlummer><<<grid, block, 0, st>>>(pk, part, L); break;
+        case kAdaptive: force_near64_kernel<kAdaptive><<<grid, block, 0, st>>>(pk, part, L); break;
+        default: return fail(NB_ERR_INVALID, "force: unknown method %d", force_method);
     }
     NB_CUDA(cudaGetLastError());
     return NB_OK;

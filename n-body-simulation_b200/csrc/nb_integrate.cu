@@ -48,7 +48,9 @@ __device__ __forceinline__ void pack_one(float* __restrict__ pk, long i, const d
     o[7 * kTJ] = (float)(p.w * inv3mbar);
 }
 
-// Bounding box of the tile this CTA just packed (one CTA == one tile of kTJ particles) -> meta row of the tile.
+// Bounding boxes of the tile this CTA just packed (one CTA == one tile of kTJ particles) -> meta row of the tile:
+//   [0..2] min, [3..5] max of the whole tile, [6] max |coordinate|,
+//   [8 + 6 sb .. 8 + 6 sb + 5] min / max of sub-tile sb (64 consecutive particles), sb = 0..3.
 __device__ __forceinline__ void tile_meta(float* __restrict__ pk, long tile, float x, float y, float z) {
     __shared__ float shm[7][kThreads / 32];
     float v[7] = {x, y, z, x, y, z, fmaxf(fabsf(x), fmaxf(fabsf(y), fabsf(z)))};
@@ -62,11 +64,17 @@ __device__ __forceinline__ void tile_meta(float* __restrict__ pk, long tile, flo
         if ((threadIdx.x & 31) == 0) shm[c][threadIdx.x >> 5] = v[c];
     }
     __syncthreads();
+    float* meta = pk + (size_t)tile * kTileFloats + kMetaRow * kTJ;
     if (threadIdx.x < 7) {
         const int c = threadIdx.x;
         float r = shm[c][0];
         for (int k = 1; k < kThreads / 32; ++k) r = c < 3 ? fminf(r, shm[c][k]) : fmaxf(r, shm[c][k]);
-        pk[(size_t)tile * kTileFloats + kMetaRow * kTJ + c] = r;
+        meta[c] = r;
+    } else if (threadIdx.x >= 32 && threadIdx.x < 32 + 24) {      // sub-tile sb = warps 2 sb and 2 sb + 1
+        const int k = threadIdx.x - 32, sb = k / 6, c = k % 6;
+        const float a = shm[c][2 * sb], b2 = shm[c][2 * sb + 1];
+        meta[kSubBoxOffset + k] = c < 3 ? fminf(a, b2) : fmaxf(a, b2);
+        (void)sb;
     }
 }
 

@@ -72,9 +72,34 @@ extent_final_kernel(const double* __restrict__ part, long nblocks, double* __res
         box[3] = 2097151.0 / ext;                  // cells of equal size in all three dimensions (2^21 - 1 per axis)
     }
 }
+// 3-D Hilbert index from three 21-bit coordinates (Skilling's transpose algorithm, "Programming the Hilbert curve",
+// AIP Conf. Proc. 707, 2004), bits interleaved into one 63-bit key. Unlike the Morton (Z) curve, consecutive keys are
+// always adjacent cells, so a run of 64 / 128 / 256 / 1024 consecutive particles is a connected, compact blob and the
+// bounding boxes the force kernel classifies tiles with overlap far less.
+__device__ __forceinline__ unsigned long long hilbert63(unsigned int x, unsigned int y, unsigned int z) {
+    unsigned int X[3] = {x, y, z};
+    const unsigned int M = 1u << 20;
+    for (unsigned int Q = M; Q > 1; Q >>= 1) {          // inverse undo
+        const unsigned int P = Q - 1;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            if (X[i] & Q) X[0] ^= P;
+            else { const unsigned int t = (X[0] ^ X[i]) & P; X[0] ^= t; X[i] ^= t; }
+        }
+    }
+#pragma unroll
+    for (int i = 1; i < 3; ++i) X[i] ^= X[i - 1];       // Gray encode
+    unsigned int t = 0;
+    for (unsigned int Q = M; Q > 1; Q >>= 1) if (X[2] & Q) t ^= Q - 1;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) X[i] ^= t;
+    // transpose -> key: bit b of X[0] is the most significant of each triple
+    return (spread21(X[0]) << 2) | (spread21(X[1]) << 1) | spread21(X[2]);
+}
+
 __global__ void __launch_bounds__(kThreads)
 morton_key_kernel(const double4* __restrict__ pos, long n, const double* __restrict__ box,
-                  unsigned long long* __restrict__ keys, unsigned int* __restrict__ idx) {
+                  unsigned long long* __restrict__ keys, unsigned int* __restrict__ idx, int curve) {
     const long i = (long)blockIdx.x * kThreads + threadIdx.x;
     if (i >= n) return;
     const double4 p = pos[i];
@@ -82,7 +107,8 @@ morton_key_kernel(const double4* __restrict__ pos, long n, const double* __restr
     const unsigned long long kx = (unsigned long long)fmin(fmax((p.x - box[0]) * s, 0.0), 2097151.0);
     const unsigned long long ky = (unsigned long long)fmin(fmax((p.y - box[1]) * s, 0.0), 2097151.0);
     const unsigned long long kz = (unsigned long long)fmin(fmax((p.z - box[2]) * s, 0.0), 2097151.0);
-    keys[i] = spread21(kx) | (spread21(ky) << 1) | (spread21(kz) << 2);
+    keys[i] = curve == 1 ? hilbert63((unsigned int)kx, (unsigned int)ky, (unsigned int)kz)
+                         : (spread21(kx) | (spread21(ky) << 1) | (spread21(kz) << 2));
     idx[i] = (unsigned int)i;
 }
 __global__ void __launch_bounds__(kThreads)
@@ -185,7 +211,7 @@ size_t sort_temp_bytes(long n) {
 
 // perm[s] = index (caller order) of the particle stored at sorted slot s. scratch: keys (2n u64), idx (n u32),
 // extent partials (6 * blocks doubles + 8), cub temp.
-int build_permutation(const double4* src_pos, long n, bool spatial, SortScratch& S, unsigned int* perm, cudaStream_t st) {
+int build_permutation(const double4* src_pos, long n, int spatial, SortScratch& S, unsigned int* perm, cudaStream_t st) {
     if (!spatial) {
         iota_kernel<<<blocks_for(n), kThreads, 0, st>>>(perm, n);
         NB_CUDA(cudaGetLastError());
@@ -195,7 +221,7 @@ int build_permutation(const double4* src_pos, long n, bool spatial, SortScratch&
     NB_CUDA(cudaGetLastError());
     extent_final_kernel<<<1, 1024, 0, st>>>(S.extent_part, (long)blocks_for(n), S.box);
     NB_CUDA(cudaGetLastError());
-    morton_key_kernel<<<blocks_for(n), kThreads, 0, st>>>(src_pos, n, S.box, S.keys_in, S.idx_in);
+    morton_key_kernel<<<blocks_for(n), kThreads, 0, st>>>(src_pos, n, S.box, S.keys_in, S.idx_in, spatial == 2 ? 0 : 1);
     NB_CUDA(cudaGetLastError());
     size_t bytes = S.cub_bytes;
     NB_CUDA(cub::DeviceRadixSort::SortPairs(S.cub_temp, bytes, S.keys_in, S.keys_out, S.idx_in, perm, (int)n, 0, 63, st));
