@@ -69,7 +69,7 @@ int nb_comm_unique_id(void* id128);                               /* 128-byte nc
 int nb_comm_init(nb_ctx* ctx, const void* id128, int rank, int world);
 
 /* Host -> device of the whole system (cuda/BenchmarkKernels.cu:40-41). Buffers may be pinned or pageable. On the device
- * the particles are kept in Morton (Z-curve) order so that a tile of 256 consecutive particles is spatially compact;
+ * the particles are kept in Hilbert-curve order so that a tile of 256 consecutive particles is spatially compact;
  * every entry point that returns per-particle data applies the inverse permutation, so callers only ever see their
  * own order. Multi-GPU: every rank uploads the whole system (all ranks must pass identical arrays). */
 int nb_upload(nb_ctx* ctx, const double* posMass4, const double* vel4);
@@ -128,7 +128,7 @@ int nb_timer_stop(nb_ctx* ctx, float* ms);
  *   "spatial_sort"     1 (default) order the particles along a 3-D Hilbert curve at upload | 2 Morton (Z) curve
  *                      | 0 keep the caller's order
  *   "collect_stats"    1 = count tile classifications (see nb_tile_stats); costs a few atomics per tile
- *   "resort_interval"  re-establish the Morton order from the current positions every so many steps (default 16; 0 never);
+ *   "resort_interval"  re-establish the curve order from the current positions every so many steps (default 16; 0 never);
  *                      results stay correct without it, but tiles that lose their compactness take the slower near path
  *   "far_kappa_milli"  1000*kappa of the far-tile criterion box gap > kappa*(half-extent_i + half-extent_j)
  *                      (default 250); 0 = every tile through the near-field path */
