@@ -112,8 +112,11 @@ int nb_last_force_ms(nb_ctx* ctx, float* ms);
 int nb_force_timing(nb_ctx* ctx, int reset, float* mean_ms, int* evals);
 /* Diagnostics of the production FP32 kernel (after nb_set_option(ctx, "collect_stats", 1), which also resets them):
  * out[0] j-tiles taken through the CTA-frame far path, out[1] j-tiles refined per warp (both counted once per CTA),
- * out[2] 64-particle sub-tiles through the warp-frame far path, out[3] sub-tiles evaluated in FP64 (once per warp). */
-int nb_tile_stats(nb_ctx* ctx, unsigned long long out[4]);
+ * out[2] 64-particle sub-tiles through the warp-frame far path, out[3] sub-tiles evaluated in FP64 (once per warp),
+ * out[4] the largest number of FP64 sub-tiles any single warp (of one j-split) has. */
+int nb_tile_stats(nb_ctx* ctx, unsigned long long out[5]);
+/* Per-(warp, j-split) FP64 sub-tile counts of the last evaluation (zero-filled beyond the launched grid). */
+int nb_tile_stats_warps(nb_ctx* ctx, unsigned long long* out, long cap, long* n_out);
 /* CUDA-event stopwatch on the context's stream (torch.cuda.Event only sees torch's own streams):
  * nb_timer_start records the start event; nb_timer_stop records the stop event, waits for it and returns the device
  * time in ms of everything the context enqueued in between. */

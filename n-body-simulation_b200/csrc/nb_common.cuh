@@ -48,6 +48,7 @@ struct ForceLaunch {          // one launch = i-tiles [it0, it0+nit) against the
     long npad;                // padded particle count (row stride of `part`)
     int s0, S;                // this launch writes partial slots s0 .. s0+S-1
     float g0;                 // mass scale G * (mean mass) of the mass-scaled far path (> 0)
+    int stats_warps;           // != 0: stats has 8 + (warps x splits) words; per-warp near counts are stored from word 8
     unsigned long long* stats; // optional device counters [4]: far tiles, CTA-near tiles (per CTA), far / FP64 sub-tiles (per warp); or null
     float kappa;              // far-tile criterion: box gap > kappa * (|x|max_i + |x|max_j); huge = always accurate path
 };

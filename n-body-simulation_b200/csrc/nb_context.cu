@@ -205,10 +205,18 @@ int eval_force(nb_ctx* c, int* S_out) {
     L.kappa = c->kappa > 0.f ? c->kappa : 3.0e38f;
     L.g0 = c->avg_mass > 0.0 ? (float)(kG * c->avg_mass) : 1.f;
     L.stats = c->collect_stats ? c->stats : nullptr;
+    L.stats_warps = c->collect_stats ? 1 : 0;
     const int slot = (int)(c->fev_count % nb_ctx::kRing);
     NB_CUDA(cudaEventRecord(c->fev0[slot], c->stream));
     int S_far = 0, rc;
-    const int S_near = split_near ? splits_for(c, iblocks, c->ntiles) : 0;
+    // The near kernel's work per warp is very uneven (a warp whose 128 particles straddle a jump of the Hilbert curve has a
+    // huge box and 50x the median number of FP64 sub-tiles), so its j-range is cut finer than the far kernel's.
+    int S_near = 0;
+    if (split_near) {
+        S_near = splits_for(c, iblocks, c->ntiles);
+        const int fine = c->ntiles / 64 < 16 ? (c->ntiles / 64 > 0 ? c->ntiles / 64 : 1) : 16;
+        if (S_near < fine) S_near = fine;
+    }
     if (c->world == 1) {
         L.jt0 = 0; L.jcount = c->ntiles; L.s0 = 0; L.S = splits_for(c, iblocks, L.jcount);
         S_far = L.S;
@@ -425,8 +433,10 @@ int nb_set_option(nb_ctx* c, const char* key, long value) {
     if (!strcmp(key, "spatial_sort")) { if (value < 0 || value > 2) return fail(NB_ERR_INVALID, "spatial_sort must be 0..2"); c->spatial_sort = (int)value; return NB_OK; }
     if (!strcmp(key, "collect_stats")) {
         int rc = use_device(c); if (rc) return rc;
-        if (!c->stats) NB_CUDA(cudaMalloc(&c->stats, 4 * sizeof(unsigned long long)));
-        NB_CUDA(cudaMemsetAsync(c->stats, 0, 4 * sizeof(unsigned long long), c->stream));
+        // 8 counters + one word per (warp, j-split) of the far kernel (at most 64 splits)
+        const size_t words = 8 + (size_t)(c->npad / 128) * 64;
+        if (!c->stats) NB_CUDA(cudaMalloc(&c->stats, words * sizeof(unsigned long long)));
+        NB_CUDA(cudaMemsetAsync(c->stats, 0, words * sizeof(unsigned long long), c->stream));
         c->collect_stats = value ? 1 : 0;
         return NB_OK;
     }
@@ -639,12 +649,26 @@ int nb_force_timing(nb_ctx* c, int reset, float* mean_ms, int* evals) {
     return NB_OK;
 }
 
-int nb_tile_stats(nb_ctx* c, unsigned long long out[4]) {
+int nb_tile_stats(nb_ctx* c, unsigned long long out[5]) {
     if (!c || !out) return fail(NB_ERR_INVALID, "nb_tile_stats: NULL argument");
     if (!c->stats) return fail(NB_ERR_INVALID, "nb_tile_stats: enable with nb_set_option(ctx, \"collect_stats\", 1) first");
     int rc = use_device(c); if (rc) return rc;
-    NB_CUDA(cudaMemcpyAsync(out, c->stats, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaMemcpyAsync(out, c->stats, 5 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+// Per-warp FP64 sub-tile counts of the last force evaluation (collect_stats): out[k] for k < count; returns how many
+// (warp, split) entries exist through *n_out.
+int nb_tile_stats_warps(nb_ctx* c, unsigned long long* out, long cap, long* n_out) {
+    if (!c || !out || !n_out) return fail(NB_ERR_INVALID, "nb_tile_stats_warps: NULL argument");
+    if (!c->stats) return fail(NB_ERR_INVALID, "nb_tile_stats_warps: enable collect_stats first");
+    int rc = use_device(c); if (rc) return rc;
+    const long words = (long)(c->npad / 128) * 64;
+    const long nn = words < cap ? words : cap;
+    NB_CUDA(cudaMemcpyAsync(out, c->stats + 8, (size_t)nn * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    *n_out = words;
     return NB_OK;
 }
 

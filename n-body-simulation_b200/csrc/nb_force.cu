@@ -410,6 +410,10 @@ force_fp32_tma_kernel(const float* __restrict__ pk, double* __restrict__ part, c
 // * FP64 there is also what keeps the result accurate when two close neighbours pull in opposite directions (pair terms
 //   100x larger than their sum): those terms are exact to ~1e-15 instead of ~1e-7.
 // * FP32 partial sums are flushed every 128 j into FP64 sums kept in shared memory (thread-private slots).
+#ifndef NB_FAR_UNROLL
+#define NB_FAR_UNROLL 2
+#endif
+constexpr int kFarUnroll = NB_FAR_UNROLL;   // j4 groups per iteration of the far loop
 constexpr int kR4 = 4;
 constexpr int kFarFloats = 4 * kTJ;                         // rows k x', k y', k z', k  (PAIRWISE/PLUMMER)  |  x', y', z', -  (ADAPTIVE)
 constexpr int kXfFloats = kFarFloats;
@@ -625,6 +629,7 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
             Tf[c * kTJ + t] = ((xh - F.O[c]) + xl) * kj;
         }
     };
+    int near_count = 0;                        // (warp, sub-tile) pairs left to the near kernel (diagnostics)
     if (cnt > 0) { mbar_wait(&full[0], 0u); prepare(0); }
     __syncthreads();
     for (int q = 0; q < cnt; ++q) {
@@ -642,7 +647,7 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
             // ---- far tile: CTA frame, 64 j4 groups
 #pragma unroll 1
             for (int half = 0; half < 2; ++half) {
-#pragma unroll 2
+#pragma unroll kFarUnroll
                 for (int j4 = half * (kTJ / 8); j4 < (half + 1) * (kTJ / 8); ++j4) far_j4<MODE, kTJ>(S, Tf, rw, j4);
                 flush4<MODE>(S, dacc, t, L.g0);
             }
@@ -655,6 +660,7 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
                 const bool far_w = boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2);
                 const int j0 = sb * kSubTile;
                 if (L.stats && lane == 0) atomicAdd(L.stats + (far_w ? 2 : 3), 1ULL);
+                if (!far_w) ++near_count;
                 if (far_w) {
                     __syncwarp();
 #pragma unroll
@@ -679,6 +685,10 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
             mbar_expect_tx(&full[b], kTileBytes);
             bulk_g2s(raw + b * kTileFloats, pk + (size_t)wrap_tile(L.jt0 + k0 + q + kStages, L.ntiles) * kTileFloats, kTileBytes, &full[b]);
         }
+    }
+    if (L.stats && lane == 0) {
+        atomicMax(L.stats + 4, (unsigned long long)near_count);
+        if (L.stats_warps) L.stats[8 + ((size_t)s * gridDim.x + blockIdx.x) * (kThreads / 32) + (t >> 5)] = (unsigned long long)near_count;
     }
     double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad + i_first;
 #pragma unroll
@@ -729,42 +739,54 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
             ax[r] = ay[r] = az[r] = 0.0;
         }
     }
-    for (int k = k0; k < k1; ++k) {
-        const float* tile = pk + (size_t)wrap_tile(L.jt0 + k, L.ntiles) * kTileFloats;
-        const float* meta = tile + kMetaRow * kTJ;
-        if (boxes_far(Fbox, Fhalf, meta, meta + 3, L.kappa, min_gap2)) continue;       // whole tile: far kernel, CTA frame
-#pragma unroll 1
-        for (int sb = 0; sb < kTJ / kSubTile; ++sb) {
-            const float* sbox = meta + kSubBoxOffset + 6 * sb;
-            if (boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) continue;      // far kernel, warp frame
-            __syncwarp();
-#pragma unroll
-            for (int q = lane; q < kSubTile; q += 32) {
-                const float* pj = tile + sb * kSubTile + q;
-                Jw[w][0][q] = ((double)pj[0 * kTJ] - (double)Ow[0]) + (double)pj[4 * kTJ];
-                Jw[w][1][q] = ((double)pj[1 * kTJ] - (double)Ow[1]) + (double)pj[5 * kTJ];
-                Jw[w][2][q] = ((double)pj[2 * kTJ] - (double)Ow[2]) + (double)pj[6 * kTJ];
-                Jw[w][3][q] = (double)pj[3 * kTJ] + (double)pj[kGmLoRow * kTJ];
-                if (IS_ADAPTIVE(MODE)) Mq[w][q] = pj[7 * kTJ];
-            }
-            __syncwarp();
-#pragma unroll 2
-            for (int j = 0; j < kSubTile; ++j) {
-                const double xj = Jw[w][0][j], yj = Jw[w][1][j], zj = Jw[w][2][j], gm = Jw[w][3][j];
-                const double mqj = IS_ADAPTIVE(MODE) ? (double)Mq[w][j] : 0.0;
-#pragma unroll
-                for (int r = 0; r < kR4; ++r) {
-                    const double dx = xj - xi[r], dy = yj - yi[r], dz = zj - zi[r];
-                    const double r2 = dx * dx + dy * dy + dz * dz;
-                    double s2 = r2;
-                    if (IS_ADAPTIVE(MODE)) {
-                        const double wq = pow23(mqi[r] + mqj);
-                        s2 = fmax(fma(r2 * wq, 1e-4, r2), r2 + 1e-8);
+    // Scan the j-range 32 tiles at a time: lane l tests tile base + l against the CTA box (the far kernel's first-level
+    // test); the warp then visits only the tiles that need refinement (~2 % at N = 1M).
+    for (int base = k0; base < k1; base += 32) {
+        const int kk = base + lane;
+        bool refine = false;
+        if (kk < k1) {
+            const float* m = pk + (size_t)wrap_tile(L.jt0 + kk, L.ntiles) * kTileFloats + kMetaRow * kTJ;
+            refine = !boxes_far(Fbox, Fhalf, m, m + 3, L.kappa, min_gap2);
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, refine);
+        while (todo) {
+            const int k = base + (__ffs(todo) - 1);
+            todo &= todo - 1;
+            const float* tile = pk + (size_t)wrap_tile(L.jt0 + k, L.ntiles) * kTileFloats;
+            const float* meta = tile + kMetaRow * kTJ;
+    #pragma unroll 1
+            for (int sb = 0; sb < kTJ / kSubTile; ++sb) {
+                const float* sbox = meta + kSubBoxOffset + 6 * sb;
+                if (boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) continue;      // far kernel, warp frame
+                __syncwarp();
+    #pragma unroll
+                for (int q = lane; q < kSubTile; q += 32) {
+                    const float* pj = tile + sb * kSubTile + q;
+                    Jw[w][0][q] = ((double)pj[0 * kTJ] - (double)Ow[0]) + (double)pj[4 * kTJ];
+                    Jw[w][1][q] = ((double)pj[1 * kTJ] - (double)Ow[1]) + (double)pj[5 * kTJ];
+                    Jw[w][2][q] = ((double)pj[2 * kTJ] - (double)Ow[2]) + (double)pj[6 * kTJ];
+                    Jw[w][3][q] = (double)pj[3 * kTJ] + (double)pj[kGmLoRow * kTJ];
+                    if (IS_ADAPTIVE(MODE)) Mq[w][q] = pj[7 * kTJ];
+                }
+                __syncwarp();
+    #pragma unroll 2
+                for (int j = 0; j < kSubTile; ++j) {
+                    const double xj = Jw[w][0][j], yj = Jw[w][1][j], zj = Jw[w][2][j], gm = Jw[w][3][j];
+                    const double mqj = IS_ADAPTIVE(MODE) ? (double)Mq[w][j] : 0.0;
+    #pragma unroll
+                    for (int r = 0; r < kR4; ++r) {
+                        const double dx = xj - xi[r], dy = yj - yi[r], dz = zj - zi[r];
+                        const double r2 = dx * dx + dy * dy + dz * dz;
+                        double s2 = r2;
+                        if (IS_ADAPTIVE(MODE)) {
+                            const double wq = pow23(mqi[r] + mqj);
+                            s2 = fmax(fma(r2 * wq, 1e-4, r2), r2 + 1e-8);
+                        }
+                        if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
+                        double sc = gm_inv_r3(s2, gm);
+                        if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
+                        ax[r] = fma(sc, dx, ax[r]); ay[r] = fma(sc, dy, ay[r]); az[r] = fma(sc, dz, az[r]);
                     }
-                    if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
-                    double sc = gm_inv_r3(s2, gm);
-                    if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
-                    ax[r] = fma(sc, dx, ax[r]); ay[r] = fma(sc, dy, ay[r]); az[r] = fma(sc, dz, az[r]);
                 }
             }
         }

@@ -135,7 +135,7 @@ extern "C" int nb_force_noalloc(int force_method, const double* d_posMass4, doub
     NB_CUDA(cudaGetLastError());
 
     ForceLaunch L;
-    L.it0 = 0; L.nit = ntiles; L.jt0 = 0; L.jcount = ntiles; L.ntiles = ntiles; L.npad = npad; L.s0 = 0; L.S = S; L.kappa = 3.0e38f; L.g0 = 1.f; L.stats = nullptr;
+    L.it0 = 0; L.nit = ntiles; L.jt0 = 0; L.jcount = ntiles; L.ntiles = ntiles; L.npad = npad; L.s0 = 0; L.S = S; L.kappa = 3.0e38f; L.g0 = 1.f; L.stats = nullptr; L.stats_warps = 0;
     rc = launch_force_fp32(pk, part, L, force_method, /*variant=*/1, st); if (rc) return rc;
 
     noalloc_reduce_kernel<<<(unsigned)((n + kThreads - 1) / kThreads), kThreads, 0, st>>>(part, S, npad, n, reinterpret_cast<double4*>(d_accel4));

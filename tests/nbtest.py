@@ -6,7 +6,7 @@ import os
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-LIB_PATH = os.path.join(ROOT, "n-body-simulation_b200", "libnbody_b200.so")
+LIB_PATH = os.environ.get("NB_LIB_PATH", os.path.join(ROOT, "n-body-simulation_b200", "libnbody_b200.so"))
 ORACLE_PATH = os.path.join(ROOT, "oracle", "libnboracle.so")
 REF_PATH = os.path.join(ROOT, "oracle", "_ref", "libnbref.so")
 
