@@ -90,7 +90,7 @@ def ncu_traffic_bytes(n, force, prec, world):
     (profiles/), valid for the default workload only; None otherwise."""
     if not (n == 1048576 and force == nbtest.PAIRWISE and prec == nbtest.FP32 and world == 1):
         return None
-    path = os.path.join(ROOT, "profiles", "r01_ncu_force_fp32_r4_production.txt")
+    path = os.path.join(ROOT, "profiles", "r01_ncu_force_far_near_production.txt")
     try:
         tot = 0.0
         for line in open(path):
@@ -315,10 +315,12 @@ def main():
                     "achieved": ach_int * SLOTS_PER_INTERACTION * 2 / 1e12,
                     "peak": peak_int * SLOTS_PER_INTERACTION * 2 / 1e12, "unit": "TFLOP/s",
                     "frac": ach_int / peak_int, "traffic": ncu_traffic_bytes(n, force, prec, world),
-                    "traffic_note": "DRAM bytes per launch from profiles/r01_ncu_force_fp32_r4_production.txt; the kernel's "
-                                    "operands are 42 MB of packed tiles re-read from L2 by every CTA + 50 MB of partial sums",
+                    "traffic_note": "DRAM bytes per force evaluation (far + near kernel) from "
+                                    "profiles/r01_ncu_force_far_near_production.txt: 42 MB of packed tiles re-read from L2 by every "
+                                    "CTA, ~430 MB of partial-sum slots written (the near kernel's 16 slots dominate)",
                     "achieved_Tint_per_s": ach_int / 1e12, "peak_Tint_per_s": peak_int / 1e12,
-                    "kernel": "force_fp32 (per-GPU launch time from CUDA events on the context stream)",
+                    "kernel": "force evaluation = force_fp32_r4_kernel (far, FP32) + force_near64_kernel (near, FP64, own stream); "
+                              "per-GPU time from CUDA events on the context stream around both",
                     "kernel_ms": fk_ms, "share_of_step": fk_ms / (t_step * 1e3),
                     "peak_source": f"{n_sm} SMs x 128 FP32 lanes x sm_max_mhz from {peak_src}; no FP32 entry in "
                                    f"MEASURED_PEAKS.json (tools/pipe_bench measures the FFMA/FFMA2/MUFU rates)",
