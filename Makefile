@@ -6,7 +6,7 @@ LIB    := $(PKG)/libnbody_b200.so
 ARCH   := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS:= $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Iinclude -I$(CSRC) --expt-relaxed-constexpr
 
-CU_SRCS := $(CSRC)/nb_force.cu $(CSRC)/nb_integrate.cu $(CSRC)/nb_sort.cu $(CSRC)/nb_context.cu $(CSRC)/nb_noalloc.cu
+CU_SRCS := $(CSRC)/nb_force.cu $(CSRC)/nb_integrate.cu $(CSRC)/nb_sort.cu $(CSRC)/nb_context.cu $(CSRC)/nb_noalloc.cu $(CSRC)/nb_render.cu
 CU_OBJS := $(CU_SRCS:.cu=.o)
 
 .PHONY: all lib oracle ref refgpu refcuda tools host clean

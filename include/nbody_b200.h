@@ -102,6 +102,18 @@ int nb_average_mass(nb_ctx* ctx, double* out);
  * NULL): n x (id, mass). Host pointers. */
 int nb_snapshot(nb_ctx* ctx, double time, double* particleData6, double* systemData2, double* staticData2);
 
+/* Headless image of the current state: the arithmetic of the reference viewer's shaders and fixed-function state
+ * (visualization/ShaderManager.cpp:147-384, CameraController.cpp:35-102, ParticleRenderer.cpp:233-306,414-465,
+ * visualization/cuda/VisualizationKernels.cu:28-49) evaluated by CUDA kernels into an RGBA8 image (rows top-down), since the
+ * target machine has no graphics stack. Camera: rot_x, rot_y, distance, translate_x/y (defaults of the reference: 0.2, 0.9,
+ * 5, 0, 0); scale <= 0: 2 / max |r| (core/System.cpp:236-248); point_size <= 0: 30; color_mode 0 UNIFORM | 1
+ * VELOCITY_MAGNITUDE; color4 / clear4 NULL: (1,1,1,0.9) / (0.02,0.02,0.05,1). The mass range is taken at the first call
+ * and the colour-ramp maximum speed is the 0.9/0.1 moving average over calls, as in the reference. info4 (may be NULL)
+ * receives (min mass, max mass, max speed used, scale used). */
+int nb_render(nb_ctx* ctx, int width, int height, float rot_x, float rot_y, float distance, float translate_x, float translate_y,
+              float scale, float point_size, int color_mode, const float* color4, const float* clear4, unsigned char* rgba8,
+              float* info4);
+
 /* Kernel launches enqueued by this context since creation (force + integrator + reduction kernels). */
 long nb_launch_count(nb_ctx* ctx);
 /* Duration in ms of the most recent force-kernel launch(es) of one force evaluation, measured with CUDA events on the

@@ -107,4 +107,12 @@ int launch_scatter_acc(const double* acc, long npad, const unsigned int* perm, l
 int launch_snapshot_scatter(const double4* pos, const double4* vel, const unsigned int* perm, long n,
                             double* particleData6, double* staticData2, cudaStream_t st);
 
+
+// nb_render.cu
+struct RenderState { bool have_mass = false; float min_mass = 1.f, max_mass = 1.f; bool have_vel = false; float smoothed = 0.f; };
+int render_splat(const double4* pos, const double4* vel, const unsigned int* perm, long n, int W, int H,
+                 float rot_x, float rot_y, float distance, float tx, float ty, float scale, float point_size, int color_mode,
+                 const float color4[4], const float clear4[4], RenderState& st, float* range_out4, unsigned char* h_rgba,
+                 cudaStream_t stream);
+
 } // namespace nb

@@ -78,6 +78,7 @@ struct nb_ctx {
     int spatial_sort = 1; float kappa = 0.25f;
     int resort_interval = 16; long steps_since_sort = 0;   // re-establish the Morton order every so many steps
     unsigned int* perm2 = nullptr;
+    RenderState render_state;
     int collect_stats = 0; unsigned long long* stats = nullptr;   // optional tile-classification counters (device, 4 words)
     double *acc = nullptr, *part = nullptr, *red_part = nullptr, *red = nullptr, *eout = nullptr;
     float* pk = nullptr;
@@ -617,6 +618,23 @@ int nb_snapshot(nb_ctx* c, double time, double* particleData6, double* systemDat
     if (staticData2) NB_CUDA(cudaMemcpyAsync(staticData2, d2, (size_t)c->n * 2 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
+}
+
+int nb_render(nb_ctx* c, int width, int height, float rot_x, float rot_y, float distance, float translate_x, float translate_y,
+              float scale, float point_size, int color_mode, const float* color4, const float* clear4, unsigned char* rgba8,
+              float* info4) {
+    if (!c || !rgba8) return fail(NB_ERR_INVALID, "nb_render: NULL argument");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_render before nb_upload");
+    if (c->world > 1) return fail(NB_ERR_UNSUPPORTED, "nb_render needs the whole system on one device");
+    if (color_mode != 0 && color_mode != 1) return fail(NB_ERR_INVALID, "nb_render: color_mode %d", color_mode);
+    int rc = use_device(c); if (rc) return rc;
+    const float white[4] = {1.0f, 1.0f, 1.0f, 0.9f};            // ParticleRenderer.cpp:36-39
+    const float night[4] = {0.02f, 0.02f, 0.05f, 1.0f};         // VisualizationUtils.cpp:101
+    rc = render_splat(c->pos, c->vel, c->perm, c->n, width, height, rot_x, rot_y, distance, translate_x, translate_y, scale,
+                      point_size > 0.f ? point_size : 30.0f, color_mode, color4 ? color4 : white, clear4 ? clear4 : night,
+                      c->render_state, info4, rgba8, c->stream);
+    if (!rc) c->launches += 6;
+    return rc;
 }
 
 long nb_launch_count(nb_ctx* c) { return c ? c->launches : 0; }
