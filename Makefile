@@ -32,7 +32,7 @@ tools/pipe_bench: tools/pipe_bench.cu
 	$(NVCC) $(ARCH) -O3 -std=c++17 -lineinfo -o $@ $<
 
 host: lib
-	$(MAKE) -C host
+	$(MAKE) -C $(PKG)/host
 
 clean:
 	rm -f $(CSRC)/*.o $(CSRC)/*.ptxas.log $(LIB) tools/pipe_bench

@@ -1,5 +1,5 @@
 // oracle/ref_gpu_driver.cpp — TEST INFRASTRUCTURE. Drop-in proof: the reference's UNMODIFIED System.cpp / Forces.cpp /
-// Initializer.cpp linked against host/ref_shims.cpp + libnbody_b200.so instead of the reference's CUDA drivers.
+// Initializer.cpp linked against n-body-simulation_b200/host/ref_shims.cpp + libnbody_b200.so instead of the reference's CUDA drivers.
 // Runs the same Particles through System(..., ExecutionMode::GPU).runBenchmark (-> runBenchmarkOnGPU -> the B200 library)
 // and through System(..., ExecutionMode::CPU).runBenchmark (the reference's OpenMP path) and prints the differences.
 //   usage: ref_system_on_b200 <n> <steps> <dt> <force 0|2> <integ 0|1> [sistema.dat path]

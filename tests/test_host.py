@@ -1,5 +1,5 @@
-"""The C++17 host drop-in (host/): config.json surface, generators, BENCHMARK / FILE_CSV sinks, and the reference's own
-System.cpp linked against host/ref_shims.cpp. CPU tests need no GPU; the gpu-marked ones run the binaries on the box."""
+"""The C++17 host drop-in (n-body-simulation_b200/host/): config.json surface, generators, BENCHMARK / FILE_CSV sinks, and the reference's own
+System.cpp linked against n-body-simulation_b200/host/ref_shims.cpp. CPU tests need no GPU; the gpu-marked ones run the binaries on the box."""
 import ctypes as C
 import json
 import os
@@ -195,7 +195,7 @@ def test_host_file_csv_mode(tmp_path, host, oracle):
 @pytest.mark.gpu
 @pytest.mark.parametrize("prec,tol", [("0", 2e-5), ("1", 1e-9)], ids=["fp32", "fp64"])
 def test_reference_system_cpp_runs_on_the_b200_library(prec, tol):
-    """The reference's own System.cpp/Forces.cpp, linked with host/ref_shims.cpp: System(GPU).runBenchmark goes through
+    """The reference's own System.cpp/Forces.cpp, linked with n-body-simulation_b200/host/ref_shims.cpp: System(GPU).runBenchmark goes through
     runBenchmarkOnGPU -> nb_run_benchmark and lands on the same state as the reference's CPU/OpenMP run."""
     if not os.path.exists(REF_BIN):
         pytest.skip("oracle/_ref/ref_system_on_b200 not built (reference tree absent at build time)")
