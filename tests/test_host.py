@@ -193,6 +193,29 @@ def test_host_file_csv_mode(tmp_path, host, oracle):
 
 
 @pytest.mark.gpu
+def test_host_checkpoint_resume(tmp_path, host, oracle):
+    """"snapshotOut" + FROM_FILE *.nbin: 10 steps, checkpoint, 10 more steps == 20 steps of the CPU integrator."""
+    snap1, snap2 = str(tmp_path / "a.nbin"), str(tmp_path / "b.nbin")
+    base = json.loads(cfg_text(seed=11, years=0.1, dtYears=0.01, precision="FP64").split("\n#")[0])
+    base["init"]["RANDOM"]["nParticles"] = 200
+    base["snapshotOut"] = snap1
+    (tmp_path / "config.json").write_text(json.dumps(base))
+    assert subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300).returncode == 0
+    base["init"]["selected"] = "FROM_FILE"
+    base["init"]["FROM_FILE"] = {"filePath": snap1, "partialCount": 0}
+    base["snapshotOut"] = snap2
+    (tmp_path / "config.json").write_text(json.dumps(base))
+    assert subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300).returncode == 0
+    raw = np.fromfile(snap2, dtype=np.float64, offset=16)
+    pm2, v2 = raw[:800].reshape(200, 4), raw[800:].reshape(200, 4)
+    start = json.loads(cfg_text(seed=11).split("\n#")[0]); start["init"]["RANDOM"]["nParticles"] = 200
+    pm0, v0, _ = init_from(host, json.dumps(start))
+    p_ref, v_ref = oracle.step(pm0, v0, nbtest.VV, nbtest.PAIRWISE, 0.01, 20)
+    np.testing.assert_allclose(pm2[:, :3], p_ref[:, :3], atol=1e-9)
+    np.testing.assert_allclose(v2[:, :3], v_ref[:, :3], atol=1e-9)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("prec,tol", [("0", 2e-5), ("1", 1e-9)], ids=["fp32", "fp64"])
 def test_reference_system_cpp_runs_on_the_b200_library(prec, tol):
     """The reference's own System.cpp/Forces.cpp, linked with n-body-simulation_b200/host/ref_shims.cpp: System(GPU).runBenchmark goes through
