@@ -1,7 +1,9 @@
 // nbh_capi.cpp — plain-C exports of the host layer (libnbody_host.so) so that tests and bench.py can call the C++
 // generators / config parser / run driver through ctypes. All functions return 0 on success; nbh_last_error() has the text.
 #include <cstring>
+#include <stdexcept>
 #include <string>
+#include <vector>
 
 #include "nbh_host.hpp"
 
@@ -47,5 +49,36 @@ int nbh_parse_config(const char* config_text, long out[8]) {
 int nbh_run_config(const char* config_text, double* run_seconds, long* n_out, long* steps_out) {
     return guard([&] { nbh::Config c = nbh::parse_config_text(config_text); nbh::RunReport r = nbh::run_config(c, true);
                        if (run_seconds) *run_seconds = r.run_seconds; if (n_out) *n_out = (long)r.n; if (steps_out) *steps_out = r.steps; return 0; });
+}
+// --auto-benchmark pieces. out5 = mean, std, min, max, cv (core/main.cpp:52-80).
+int nbh_sample_stats(const double* values, long count, double out5[5]) {
+    return guard([&] { nbh::SampleStats s = nbh::sample_stats(std::vector<double>(values, values + count));
+                       out5[0] = s.mean; out5[1] = s.std; out5[2] = s.min; out5[3] = s.max; out5[4] = s.cv; return 0; });
+}
+double nbh_sweep_years_for(int n) { return nbh::sweep_years_for(n); }
+// CSV text for one synthetic result whose per-run execution times are given (no GPU involved): checks schema + formats.
+int nbh_sweep_csv_from_times(int n, double years, double dt, int force, int integ, const double* secs, long runs, char* out, long cap) {
+    return guard([&] { nbh::SweepResult r; r.params.numParticles = n; r.params.years = years; r.params.dtYears = dt;
+                       r.params.forceMethod = (nbh::ForceMethod)force; r.params.integrationMethod = (nbh::IntegrationMethod)integ;
+                       r.numRuns = (int)runs; r.totalSteps = (long)(years / dt); r.success = true;
+                       std::vector<double> t(secs, secs + runs), sps, psps;
+                       for (double x : t) { sps.push_back((double)r.totalSteps / x); psps.push_back((double)n * (double)r.totalSteps / x); }
+                       r.execTime = nbh::sample_stats(t); r.stepsPerSecond = nbh::sample_stats(sps); r.particleStepsPerSecond = nbh::sample_stats(psps);
+                       const std::string csv = nbh::sweep_csv({r});
+                       if ((long)csv.size() + 1 > cap) throw std::runtime_error("csv buffer too small");
+                       std::memcpy(out, csv.c_str(), csv.size() + 1); return 0; });
+}
+// A real sweep on the GPU; sizes[count]; CSV text into out. Returns 0 when every configuration succeeded.
+int nbh_run_sweep(const int* sizes, long count, int force, int integ, int runs, double years, double dt, unsigned long seed,
+                  int precision, char* out, long cap) {
+    return guard([&] { nbh::SweepSpec spec; spec.particleCounts.assign(sizes, sizes + count);
+                       spec.forceMethods = {(nbh::ForceMethod)force}; spec.integrationMethods = {(nbh::IntegrationMethod)integ};
+                       spec.runs = runs; spec.years = years; spec.dtYears = dt; spec.hasSeed = true; spec.seed = seed; spec.precision = precision;
+                       const std::vector<nbh::SweepResult> res = nbh::run_sweep(spec, true);
+                       const std::string csv = nbh::sweep_csv(res);
+                       if ((long)csv.size() + 1 > cap) throw std::runtime_error("csv buffer too small");
+                       std::memcpy(out, csv.c_str(), csv.size() + 1);
+                       for (const auto& r : res) if (!r.success) throw std::runtime_error(r.errorMessage);
+                       return 0; });
 }
 }

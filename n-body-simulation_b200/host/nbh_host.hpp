@@ -85,4 +85,36 @@ bool write_csv(const std::string& filename, const std::string& metadata, size_t 
 struct RunReport { double init_seconds = 0, run_seconds = 0; long steps = 0; size_t n = 0; std::string output_path; };
 RunReport run_config(const Config& cfg, bool quiet);
 
+// --auto-benchmark harness (core/main.cpp:13-452): size sweep x repeated runs on random initial conditions -> statistics
+// and a CSV with the reference's columns. Implemented in nbh_sweep.cpp.
+struct SampleStats { double mean = 0, std = 0, min = 0, max = 0, cv = 0; };
+SampleStats sample_stats(const std::vector<double>& values);
+double sweep_years_for(int numParticles);
+struct SweepCase {
+    int numParticles = 0; double years = 0, dtYears = 0.01;
+    ForceMethod forceMethod = ForceMethod::PAIRWISE; IntegrationMethod integrationMethod = IntegrationMethod::VELOCITY_VERLET;
+    int numThreads = 1; int blockSize = -1; std::string initType = "random";
+    int precision = 0; int device = -1;
+};
+struct SweepResult {
+    SweepCase params; int numRuns = 0; long totalSteps = 0;
+    SampleStats execTime, stepsPerSecond, particleStepsPerSecond;
+    bool success = false; std::string errorMessage;
+};
+struct SweepSpec {
+    std::vector<int> particleCounts{64, 128, 256, 512, 1024, 2048, 4096, 8192, 16384, 32768, 65536, 131072};   // main.cpp:295
+    std::vector<ForceMethod> forceMethods{ForceMethod::PAIRWISE};
+    std::vector<IntegrationMethod> integrationMethods{IntegrationMethod::VELOCITY_VERLET};
+    double years = 0;          // <= 0: sweep_years_for(N)
+    double dtYears = 0.01;     // main.cpp:306
+    int runs = 5;              // main.cpp:308
+    bool warm = true;          // one untimed run per configuration first
+    bool hasSeed = false; unsigned long seed = 0;
+    int precision = 0; int device = -1;
+    std::string outputFile;
+};
+SweepResult sweep_one(const SweepCase& c, int runs, const unsigned long* seed, bool warm);
+std::string sweep_csv(const std::vector<SweepResult>& results);
+std::vector<SweepResult> run_sweep(const SweepSpec& spec, bool quiet);
+
 } // namespace nbh

@@ -156,6 +156,48 @@ def test_host_binary_fails_loudly_without_gpu(tmp_path, lib):
     (tmp_path / "config.json").write_text(cfg_text(outputMode="VISUALIZATION"))
     r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True)
     assert r.returncode == 1 and "reference-only" in r.stderr
+    out = tmp_path / "s.csv"
+    r = subprocess.run([HOST_BIN, "--auto-benchmark", "--sizes", "256", "--runs", "1", "--out", str(out)], capture_output=True, text=True)
+    assert r.returncode == 2 and 'false,"no CUDA device available (there is no CPU fallback)"' in out.read_text()
+
+
+SWEEP_HEADER = ("NumParticles,Years,DtYears,ExecutionMode,ForceMethod,IntegrationMethod,NumThreads,BlockSize,InitType,"
+                "NumRuns,TotalSteps,MeanExecutionTime,StdExecutionTime,MeanStepsPerSecond,StdStepsPerSecond,CVStepsPerSecond,"
+                "MinStepsPerSecond,MaxStepsPerSecond,MeanParticleStepsPerSecond,StdParticleStepsPerSecond,Success,ErrorMessage")
+
+
+def test_auto_benchmark_statistics_and_csv_schema(host):
+    """The --auto-benchmark harness (reference core/main.cpp:52-80 statistics, :238-288 CSV, :300-304 adaptive years)."""
+    host.nbh_sample_stats.argtypes = [nbtest._dp, C.c_long, nbtest._dp]
+    host.nbh_sweep_years_for.restype = C.c_double
+    host.nbh_sweep_csv_from_times.argtypes = [C.c_int, C.c_double, C.c_double, C.c_int, C.c_int, nbtest._dp, C.c_long, C.c_char_p, C.c_long]
+    v = np.array([2.0, 4.0, 4.0, 4.0, 5.0, 5.0, 7.0, 9.0]); out = np.zeros(5)
+    assert host.nbh_sample_stats(v.ctypes.data_as(nbtest._dp), len(v), out.ctypes.data_as(nbtest._dp)) == 0
+    assert out[0] == v.mean() and abs(out[1] - v.std(ddof=1)) < 1e-15 and out[2] == 2.0 and out[3] == 9.0
+    assert abs(out[4] - v.std(ddof=1) / v.mean()) < 1e-15
+    one = np.array([3.5])
+    host.nbh_sample_stats(one.ctypes.data_as(nbtest._dp), 1, out.ctypes.data_as(nbtest._dp))
+    assert list(out) == [3.5, 0.0, 3.5, 3.5, 0.0]                       # a single run has no spread (main.cpp:72-75)
+    assert [host.nbh_sweep_years_for(n) for n in (64, 999, 1000, 9999, 10000, 131072)] == [1.5, 1.5, 0.25, 0.25, 0.1, 0.1]
+    secs = np.array([0.5, 0.25, 1.0]); buf = C.create_string_buffer(4096)
+    assert host.nbh_sweep_csv_from_times(4096, 0.25, 0.01, 1, 1, secs.ctypes.data_as(nbtest._dp), 3, buf, 4096) == 0
+    head, row = buf.value.decode().strip().split("\n")
+    assert head == SWEEP_HEADER
+    f = row.split(",")
+    assert len(f) == 22 and f[:11] == ["4096", "0.25", "0.01", "GPU", "PAIRWISE_AVX2/FP32", "VELOCITY_VERLET", "1", "-1", "random", "3", "25"]
+    sps = 25 / secs
+    assert f[11] == "%.6f" % secs.mean() and f[12] == "%.6f" % secs.std(ddof=1)
+    assert f[13] == "%.2f" % sps.mean() and f[14] == "%.2f" % sps.std(ddof=1) and f[15] == "%.4f" % (sps.std(ddof=1) / sps.mean())
+    assert f[16] == "%.2f" % sps.min() and f[17] == "%.2f" % sps.max()
+    assert f[18] == "%.3e" % (4096 * sps).mean() and f[19] == "%.3e" % (4096 * sps).std(ddof=1)
+    assert f[20] == "true" and f[21] == '""'
+
+
+def test_auto_benchmark_cli_rejects_bad_options():
+    r = subprocess.run([HOST_BIN, "--auto-benchmark", "--forces", "LEAPFROG"], capture_output=True, text=True)
+    assert r.returncode == 1 and "unknown force method" in r.stderr
+    r = subprocess.run([HOST_BIN, "--auto-benchmark", "--bogus"], capture_output=True, text=True)
+    assert r.returncode == 1 and "unknown option" in r.stderr
 
 
 @pytest.mark.gpu
@@ -167,6 +209,26 @@ def test_host_benchmark_mode(tmp_path):
     (tmp_path / "config.json").write_text(cfg_text(seed=1, forceMethod="BARNES_HUT"))
     r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
     assert r.returncode == 1 and "reference-only" in r.stderr
+
+
+@pytest.mark.gpu
+def test_auto_benchmark_sweep_on_gpu(tmp_path):
+    out = tmp_path / "sweep.csv"
+    r = subprocess.run([HOST_BIN, "--auto-benchmark", "--sizes", "256,4096", "--forces", "PAIRWISE,ADAPTIVE_MUTUAL", "--runs", "3",
+                        "--years", "0.05", "--seed", "11", "--out", str(out)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = out.read_text().strip().split("\n")
+    assert lines[0] == SWEEP_HEADER and len(lines) == 5
+    for ln, (n, fm) in zip(lines[1:], [(256, "PAIRWISE"), (256, "ADAPTIVE_MUTUAL"), (4096, "PAIRWISE"), (4096, "ADAPTIVE_MUTUAL")]):
+        f = ln.split(",")
+        assert f[0] == str(n) and f[3] == "GPU" and f[4] == fm and f[9] == "3" and f[10] == "5" and f[20] == "true"
+        assert float(f[13]) > 0 and float(f[16]) <= float(f[13]) <= float(f[17]) and float(f[18]) > 0
+    # BARNES_HUT stays reference-only: the row records the failure (Success=false + message) and the exit code is 2
+    r = subprocess.run([HOST_BIN, "--auto-benchmark", "--sizes", "256", "--forces", "BARNES_HUT", "--runs", "1", "--out", str(out)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 2
+    f = out.read_text().strip().split("\n")[1].split(",")
+    assert f[20] == "false" and "reference-only" in f[21]
 
 
 @pytest.mark.gpu
