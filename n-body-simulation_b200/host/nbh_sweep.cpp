@@ -8,6 +8,7 @@
 // first run per configuration absorbs CUDA context creation, which the reference's wall clock folds into run 0.
 #include <chrono>
 #include <cmath>
+#include <filesystem>
 #include <fstream>
 #include <iomanip>
 #include <iostream>
@@ -126,6 +127,15 @@ std::vector<SweepResult> run_sweep(const SweepSpec& spec, bool quiet) {
                 c.forceMethod = fm; c.integrationMethod = im; c.precision = spec.precision; c.device = spec.device;
                 cases.push_back(c);
             }
+    // The reference writes into presentation/benchmarks/ without creating it, so its CSV is lost when the directory is
+    // missing (main.cpp:432-436); here the directory is created and the file opened before any GPU time is spent.
+    std::ofstream csv;
+    if (!spec.outputFile.empty()) {
+        const std::filesystem::path parent = std::filesystem::path(spec.outputFile).parent_path();
+        if (!parent.empty()) std::filesystem::create_directories(parent);
+        csv.open(spec.outputFile);
+        if (!csv) throw std::runtime_error("cannot write " + spec.outputFile);
+    }
     std::vector<SweepResult> out;
     auto w0 = std::chrono::high_resolution_clock::now();
     for (size_t i = 0; i < cases.size(); ++i) {
@@ -155,10 +165,8 @@ std::vector<SweepResult> run_sweep(const SweepSpec& spec, bool quiet) {
                   << std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - w0).count() << " s, " << ok
                   << "/" << out.size() << " configurations succeeded\n";
     }
-    if (!spec.outputFile.empty()) {
-        std::ofstream f(spec.outputFile);
-        if (!f) throw std::runtime_error("cannot write " + spec.outputFile);
-        f << sweep_csv(out);
+    if (csv.is_open()) {
+        csv << sweep_csv(out);
         if (!quiet) std::cout << "Results saved to " << spec.outputFile << "\n";
     }
     return out;
