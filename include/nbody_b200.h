@@ -90,7 +90,9 @@ int nb_step(nb_ctx* ctx, double dt, int nsteps);
 int nb_sync(nb_ctx* ctx);
 
 /* out[0]=E, out[1]=kinetic, out[2]=potential with the semantics of System::computeTotalEnergy
- * (core/System.cpp:60-85: unsoftened, every pair with r>0). O(N^2) in FP64. Single-GPU contexts only. */
+ * (core/System.cpp:60-85: unsoftened, every pair with r>0). O(N^2) in FP64. Multi-GPU: collective — each rank sums the
+ * pair potential of its own slice against the whole system, the kinetic and potential sums are all-reduced, every rank
+ * receives the same three numbers. */
 int nb_energy(nb_ctx* ctx, double out[3]);
 /* out = (sum m vx, sum m vy, sum m vz, sum m). */
 int nb_momentum(nb_ctx* ctx, double out[4]);
@@ -99,7 +101,7 @@ int nb_average_mass(nb_ctx* ctx, double* out);
 
 /* FILE_CSV sink (cuda/IntegrationKernels.cu:163-197; output/OutputData.hpp:14-31,387): writes one snapshot row.
  * particleData6: n x (x,y,z,vx,vy,vz); systemData2: (time, energy) — energy is computed here; staticData2 (may be
- * NULL): n x (id, mass). Host pointers. */
+ * NULL): n x (id, mass). Host pointers. Multi-GPU: collective; every rank's buffers receive the whole system. */
 int nb_snapshot(nb_ctx* ctx, double time, double* particleData6, double* systemData2, double* staticData2);
 
 /* Headless image of the current state: the arithmetic of the reference viewer's shaders and fixed-function state

@@ -569,12 +569,17 @@ int nb_sync(nb_ctx* c) {
 int nb_energy(nb_ctx* c, double out[3]) {
     if (!c || !out) return fail(NB_ERR_INVALID, "nb_energy: NULL argument");
     if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_energy before nb_upload");
-    if (c->world > 1) return fail(NB_ERR_UNSUPPORTED, "nb_energy needs the whole system on one device (world=%d)", c->world);
     int rc = use_device(c); if (rc) return rc;
+    // Multi-GPU: collective. Every rank completes its copy of the positions, sums the pair potential of its own i-slice
+    // against all j and its slice's kinetic energy, and the two sums are all-reduced (SURVEY 8e "small collectives").
+    if (c->world > 1) { NB_CUDA(cudaStreamSynchronize(c->comm_stream)); rc = gather_state_all(c); if (rc) return rc; }
     double* pot = reinterpret_cast<double*>(c->tmp4);
-    rc = launch_potential_fp64(c->pos, pot, c->npad, c->ntiles, c->stream); if (rc) return rc;
+    rc = launch_potential_fp64(c->pos, pot, (int)(c->i0 / kTJ), (int)(c->ni / kTJ), c->ntiles, c->stream); if (rc) return rc;
     StepArrays A = arrays(c);
-    rc = launch_energy_reduce(A, pot, c->eout, c->stream); if (rc) return rc;
+    long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;
+    rc = launch_energy_partial(A, pot, b, e - b, c->eout + 4, c->stream); if (rc) return rc;
+    if (c->world > 1) NB_NCCL(nccl::AllReduce(c->eout + 4, c->eout + 4, 4, nccl::kFloat64, nccl::kSum, c->comm, c->stream));
+    rc = launch_energy_final(c->eout + 4, c->eout, c->stream); if (rc) return rc;
     c->launches += 4;
     NB_CUDA(cudaMemcpyAsync(out, c->eout, 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
@@ -604,9 +609,8 @@ int nb_average_mass(nb_ctx* c, double* out) {
 
 int nb_snapshot(nb_ctx* c, double time, double* particleData6, double* systemData2, double* staticData2) {
     if (!c || !particleData6 || !systemData2) return fail(NB_ERR_INVALID, "nb_snapshot: NULL argument");
-    if (c->world > 1) return fail(NB_ERR_UNSUPPORTED, "nb_snapshot needs the whole system on one device");
     double e[3];
-    int rc = nb_energy(c, e); if (rc) return rc;
+    int rc = nb_energy(c, e); if (rc) return rc;       // multi-GPU: collective, and leaves every rank with the complete state
     systemData2[0] = time; systemData2[1] = e[0];
     // stage through persistent device scratch: [n][6] then [n][2] (the reference keeps the whole [T][n][6] history on the
     // device, cuda/SimulationKernels.cu:204-249; here only one snapshot is ever resident)

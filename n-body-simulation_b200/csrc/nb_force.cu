@@ -857,10 +857,10 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
 
 // Per-particle potential sum_j m_j / r_ij over every pair with r > 0 (core/System.cpp:72-82), FP64.
 __global__ void __launch_bounds__(kThreads, 2)
-potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot, int ntiles) {
+potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot, int it0, int ntiles) {
     __shared__ __align__(16) double4 sm[2][kTJ];
     const int t = threadIdx.x;
-    const int itile_first = blockIdx.x * kR64;
+    const int itile_first = it0 + blockIdx.x * kR64;
     double xi[kR64], yi[kR64], zi[kR64], acc[kR64];
 #pragma unroll
     for (int r = 0; r < kR64; ++r) {
@@ -969,9 +969,11 @@ int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, in
     return NB_OK;
 }
 
-int launch_potential_fp64(const double4* pos, double* pot, long npad, int ntiles, cudaStream_t st) {
-    dim3 grid((unsigned)(npad / (kTJ * kR64))), block(kThreads);
-    potential_fp64_kernel<<<grid, block, 0, st>>>(pos, pot, ntiles);
+int launch_potential_fp64(const double4* pos, double* pot, int it0, int nit, int ntiles, cudaStream_t st) {
+    if (nit <= 0) return NB_OK;
+    if (nit % kR64) return fail(NB_ERR_INVALID, "potential: i-tile count %d not a multiple of %d", nit, kR64);
+    dim3 grid((unsigned)(nit / kR64)), block(kThreads);
+    potential_fp64_kernel<<<grid, block, 0, st>>>(pos, pot, it0, ntiles);
     NB_CUDA(cudaGetLastError());
     return NB_OK;
 }

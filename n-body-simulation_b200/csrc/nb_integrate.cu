@@ -172,11 +172,12 @@ reduce4_kernel(const double* __restrict__ red_part, long nblocks, double* __rest
 // Energy: block sums of (kinetic, m_i * pot_i, -, -) over all particles.
 __global__ void __launch_bounds__(kThreads)
 energy_partial_kernel(const double4* __restrict__ pos, const double4* __restrict__ vel, const double* __restrict__ pot,
-                      long n, double* __restrict__ red_part) {
+                      long first, long count, double* __restrict__ red_part) {
     __shared__ double sh[32];
-    const long i = (long)blockIdx.x * kThreads + threadIdx.x;
+    const long k = (long)blockIdx.x * kThreads + threadIdx.x;
     double r[4] = {0.0, 0.0, 0.0, 0.0};
-    if (i < n) {
+    if (k < count) {
+        const long i = first + k;
         const double4 p = pos[i], v = vel[i];
         r[0] = 0.5 * p.w * (v.x * v.x + v.y * v.y + v.z * v.z);   // core/System.cpp:66-70
         r[1] = p.w * pot[i];
@@ -276,12 +277,20 @@ int launch_com_final(const StepArrays& A, cudaStream_t st) {
     return NB_OK;
 }
 
-int launch_energy_reduce(const StepArrays& A, const double* pot, double* out3, cudaStream_t st) {
-    energy_partial_kernel<<<blocks_for(A.n), kThreads, 0, st>>>(A.pos, A.vel, pot, A.n, A.red_part);
+// Kinetic and potential sums over the particles [first, first+count) -> out4 = (sum 1/2 m v^2, sum m_i pot_i, 0, 0).
+// A rank of a multi-GPU run sums its own slice; the four doubles are then all-reduced before launch_energy_final.
+int launch_energy_partial(const StepArrays& A, const double* pot, long first, long count, double* out4, cudaStream_t st) {
+    const long nb = count > 0 ? (long)blocks_for(count) : 0;
+    if (nb > 0) {
+        energy_partial_kernel<<<(unsigned)nb, kThreads, 0, st>>>(A.pos, A.vel, pot, first, count, A.red_part);
+        NB_CUDA(cudaGetLastError());
+    }
+    reduce4_kernel<<<1, 1024, 0, st>>>(A.red_part, nb, out4);
     NB_CUDA(cudaGetLastError());
-    reduce4_kernel<<<1, 1024, 0, st>>>(A.red_part, (long)blocks_for(A.n), out3 + 4);
-    NB_CUDA(cudaGetLastError());
-    energy_final_kernel<<<1, 1, 0, st>>>(out3 + 4, out3);
+    return NB_OK;
+}
+int launch_energy_final(const double* in4, double* out3, cudaStream_t st) {
+    energy_final_kernel<<<1, 1, 0, st>>>(in4, out3);
     NB_CUDA(cudaGetLastError());
     return NB_OK;
 }

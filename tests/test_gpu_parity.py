@@ -365,3 +365,27 @@ def test_full_size_configs(lib, oracle, n, gen, force, prec):
         tot = (pm[:, 3:4] * a[:, :3]).sum(0)
         scale = np.abs(pm[:, 3:4] * a[:, :3]).sum(0)
         assert np.all(np.abs(tot) <= 2e-6 * scale)
+
+
+@pytest.mark.parametrize("n,prec", [(262144, FP32), (1048576, FP32), (65536, FP64)], ids=["262144-fp32", "1M-fp32", "65536-fp64"])
+def test_symmetries_at_full_size(lib, n, prec):
+    """Size-independent properties of the all-pairs sum (no oracle needed): the result must not depend on the caller's
+    particle order, on where the origin is, and must be linear in the source masses."""
+    pm, v = nbtest.gen_spiral(n, seed=21)
+    a0 = gpu_accel(lib, pm, v, PAIRWISE, prec)
+    tol = 2 * TOL[prec]                                   # two evaluations, each within TOL of the exact sum
+    # 1. permutation of the input: a(P x)[k] = a(x)[P[k]]
+    perm = np.random.default_rng(3).permutation(n)
+    a1 = gpu_accel(lib, np.ascontiguousarray(pm[perm]), np.ascontiguousarray(v[perm]), PAIRWISE, prec)
+    assert nbtest.rel_err(a1, a0[perm]).max() <= tol
+    # 2. translation: the shifted FP64 inputs are re-rounded by <= ulp(8192)/2 = 4.5e-13 AU, ~1e-14 of the closest separations
+    shifted = pm.copy(); shifted[:, :3] += [1024.0, -4096.0, 512.0]
+    a2 = gpu_accel(lib, shifted, v, PAIRWISE, prec)
+    assert nbtest.rel_err(a2, a0).max() <= (tol if prec == FP32 else 2e-11)
+    # 3. linearity in the masses: scaling every mass by 8 scales every acceleration by 8
+    heavy = pm.copy(); heavy[:, 3] *= 8.0
+    a3 = gpu_accel(lib, heavy, v, PAIRWISE, prec)
+    assert nbtest.rel_err(a3, 8.0 * a0).max() <= tol
+    # 4. Newton's third law
+    tot = (pm[:, 3:4] * a0[:, :3]).sum(0); scale = np.abs(pm[:, 3:4] * a0[:, :3]).sum(0)
+    assert np.all(np.abs(tot) <= (2e-6 if prec == FP32 else 1e-12) * scale)
