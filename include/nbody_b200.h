@@ -169,7 +169,8 @@ int nb_run_simulation(long n, double* posMass4, double* vel4, int integration_me
 /* ---- device-pointer entry points: the inner boundary of the reference drivers ------------------------------------ */
 /* launchForceKernel(method, blocks, blockSize, smem, stream, d_posMass, d_accel, avgMass, n)
  * (cuda/ForceKernels.cu:208-232). d_posMass4 / d_accel4 are caller-owned device double4 arrays; the context provides
- * the packed-tile scratch. avg_mass <= 0: computed on the device. stream: cudaStream_t (NULL = context stream). */
+ * the packed-tile scratch. avg_mass <= 0: computed on the device. stream: cudaStream_t (NULL = context stream).
+ * The call replaces the context's particle state: nb_step afterwards needs a fresh nb_upload. */
 int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, double* d_accel4,
                     double avg_mass, long n, void* stream);
 

@@ -61,13 +61,13 @@ static long round_up(long v, long m) { return (v + m - 1) / m * m; }
 using namespace nb;
 
 struct nb_ctx {
-    int device = 0, precision = NB_PREC_FP32;
+    int device = 0, precision = NB_PREC_FP32, sm_count = 148;
     long n = 0, npad = 0; int ntiles = 0;
     int integ = NB_INTEG_VELOCITY_VERLET, force = NB_FORCE_PAIRWISE, subtract_com = 1;
     int rank = 0, world = 1; long i0 = 0, ni = 0;
     cudaStream_t stream = nullptr, comm_stream = nullptr, near_stream = nullptr;
     cudaEvent_t ev_force_begin = nullptr, ev_near_done = nullptr;
-    cudaEvent_t ev_packed = nullptr, ev_gathered = nullptr, tev0 = nullptr, tev1 = nullptr;
+    cudaEvent_t ev_packed = nullptr, ev_gathered = nullptr, ev_user = nullptr, tev0 = nullptr, tev1 = nullptr;
     static constexpr int kRing = 64;
     cudaEvent_t fev0[kRing] = {}, fev1[kRing] = {};   // ring of force-evaluation event pairs
     long fev_count = 0;
@@ -97,6 +97,7 @@ void free_arrays(nb_ctx* c) {
     cudaFree(c->acc); cudaFree(c->part); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->perm); cudaFree(c->perm2); cudaFree(c->snap);
     cudaFree(c->ss.keys_in); cudaFree(c->ss.keys_out); cudaFree(c->ss.idx_in); cudaFree(c->ss.extent_part);
     cudaFree(c->ss.box); cudaFree(c->ss.cub_temp);
+    cudaFree(c->stats); c->stats = nullptr; c->collect_stats = 0;       // sized by npad as well
     c->pos = c->vel = c->tmp4 = c->stage_pos = c->stage_vel = nullptr;
     c->acc = c->part = c->red_part = c->snap = nullptr; c->pk = nullptr; c->perm = nullptr; c->perm2 = nullptr; c->part_bytes = 0;
     c->ss = SortScratch();
@@ -159,9 +160,9 @@ int check_force_method(int force) {
 int splits_for(nb_ctx* c, int iblocks, int jcount) {
     if (c->j_splits > 0) return c->j_splits < jcount ? c->j_splits : jcount;
     // All CTAs of a launch do the same amount of work (jcount / S tiles for 512 i-particles), so the launch runs in
-    // ceil(CTAs / 296) waves of 148 SMs x 2 resident CTAs. Pick the S whose last wave is fullest, among those that give
-    // at least ~4 waves; ties go to the smaller S (less partial-sum traffic).
-    const double slots = 148.0 * 2.0;
+    // ceil(CTAs / slots) waves of sm_count SMs (148 on B200) x 2 resident CTAs. Pick the S whose last wave is fullest,
+    // among those that give at least ~4 waves; ties go to the smaller S (less partial-sum traffic).
+    const double slots = (double)c->sm_count * 2.0;
     int best = 1; double best_eff = -1.0;
     for (int S = 1; S <= 32 && S <= jcount; ++S) {
         const double waves = (double)iblocks * S / slots;
@@ -281,11 +282,7 @@ int reduce_com(nb_ctx* c) {
     return NB_OK;
 }
 
-// Particles move, so the Morton order established at upload decays and with it the compactness of the tiles (the
-// result stays correct — more tiles simply take the FP64 near path). Every resort_interval steps the order is rebuilt from
-// the current positions: x, v, a and the caller-order permutation are permuted consistently and the tiles re-packed.
-// Multi-GPU: the slices are gathered first, every rank then sorts the identical full state.
-// Multi-GPU: make every rank's copy of the (Morton-ordered) master state complete before it leaves the device.
+// Multi-GPU: make every rank's copy of the (curve-ordered) master state complete before it leaves the device.
 int gather_state_all(nb_ctx* c) {
     if (c->world == 1) return NB_OK;
     const size_t count = (size_t)c->ni * 4;
@@ -294,6 +291,10 @@ int gather_state_all(nb_ctx* c) {
     return NB_OK;
 }
 
+// Particles move, so the space-filling-curve order established at upload decays and with it the compactness of the tiles
+// (the result stays correct — more tiles simply take the FP64 near path). Every resort_interval steps the order is rebuilt
+// from the current positions: x, v, a and the caller-order permutation are permuted consistently and the tiles re-packed.
+// Multi-GPU: the slices are gathered first, every rank then sorts the identical full state.
 int resort(nb_ctx* c) {
     if (!c->spatial_sort) return NB_OK;
     int rc;
@@ -372,6 +373,7 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
     if (prop.major != 10) return fail(NB_ERR_NO_DEVICE, "device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
     nb_ctx* c = new nb_ctx();
     c->device = device; c->precision = precision; c->n = n;
+    if (prop.multiProcessorCount > 0) c->sm_count = prop.multiProcessorCount;
     c->npad = round_up(n, kAlign); c->ntiles = (int)(c->npad / kTJ);
     c->i0 = 0; c->ni = c->npad;
     auto bail = [&](int rc) { nb_destroy(c); return rc; };
@@ -383,6 +385,7 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
     NB_TRY(cudaEventCreateWithFlags(&c->ev_near_done, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
+    NB_TRY(cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming));
     NB_TRY(cudaEventCreate(&c->tev0)); NB_TRY(cudaEventCreate(&c->tev1));
     for (int k = 0; k < nb_ctx::kRing; ++k) { NB_TRY(cudaEventCreate(&c->fev0[k])); NB_TRY(cudaEventCreate(&c->fev1[k])); }
     NB_TRY(cudaMalloc(&c->red, 16 * sizeof(double)));
@@ -402,9 +405,10 @@ int nb_destroy(nb_ctx* c) {
     if (c->near_stream) cudaStreamSynchronize(c->near_stream);
     if (c->comm && nccl::CommDestroy) nccl::CommDestroy(c->comm);
     free_arrays(c);
-    cudaFree(c->red); cudaFree(c->eout); cudaFree(c->stats);
+    cudaFree(c->red); cudaFree(c->eout);
     if (c->ev_packed) cudaEventDestroy(c->ev_packed);
     if (c->ev_gathered) cudaEventDestroy(c->ev_gathered);
+    if (c->ev_user) cudaEventDestroy(c->ev_user);
     if (c->tev0) cudaEventDestroy(c->tev0);
     if (c->tev1) cudaEventDestroy(c->tev1);
     for (int k = 0; k < nb_ctx::kRing; ++k) { if (c->fev0[k]) cudaEventDestroy(c->fev0[k]); if (c->fev1[k]) cudaEventDestroy(c->fev1[k]); }
@@ -459,6 +463,7 @@ int nb_comm_init(nb_ctx* c, const void* id128, int rank, int world) {
     if (!c || !id128) return fail(NB_ERR_INVALID, "nb_comm_init: NULL argument");
     if (world < 1 || rank < 0 || rank >= world) return fail(NB_ERR_INVALID, "nb_comm_init: rank %d of %d", rank, world);
     if (c->uploaded) return fail(NB_ERR_INVALID, "nb_comm_init must precede nb_upload");
+    if (c->comm) return fail(NB_ERR_INVALID, "nb_comm_init: this context already has a communicator");
     int rc = use_device(c); if (rc) return rc;
     c->rank = rank; c->world = world;
     if (world == 1) { c->i0 = 0; c->ni = c->npad; return NB_OK; }
@@ -758,12 +763,12 @@ int nb_launch_force(nb_ctx* c, int force_method, const double* d_posMass4, doubl
     int rc = check_force_method(force_method); if (rc) return rc;
     rc = use_device(c); if (rc) return rc;
     cudaStream_t user = (cudaStream_t)stream;
-    // Order the context stream after the caller's stream and vice versa with events.
-    cudaEvent_t ev; NB_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-    if (user) { NB_CUDA(cudaEventRecord(ev, user)); NB_CUDA(cudaStreamWaitEvent(c->stream, ev, 0)); }
+    // Order the context stream after the caller's stream and vice versa with the context's own event.
+    if (user) { NB_CUDA(cudaEventRecord(c->ev_user, user)); NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_user, 0)); }
     NB_CUDA(cudaMemcpyAsync(c->stage_pos, d_posMass4, (size_t)n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+    // The context's particle state is replaced by these positions (velocities zero): a later nb_step needs a new nb_upload.
+    c->uploaded = false; c->have_accel = false;
     const int saved_force = c->force;
-    c->force = force_method;
     if (avg_mass > 0.0) c->avg_mass = avg_mass;
     else {
         rc = launch_mass_sum(c->stage_pos, n, c->red_part, c->eout + 12, c->stream); if (rc) return rc;
@@ -772,6 +777,7 @@ int nb_launch_force(nb_ctx* c, int force_method, const double* d_posMass4, doubl
         NB_CUDA(cudaStreamSynchronize(c->stream));
         c->avg_mass = r4[3] / (double)n;
     }
+    c->force = force_method;
     rc = ingest(c, c->stage_pos, nullptr);
     StepArrays A = arrays(c);
     if (!rc) rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream);
@@ -779,12 +785,11 @@ int nb_launch_force(nb_ctx* c, int force_method, const double* d_posMass4, doubl
     if (!rc) rc = eval_force(c, &S);
     if (!rc) rc = launch_accel_import_sum(c->part, S, c->npad, n, c->tmp4, c->stream);
     if (!rc) rc = launch_scatter4(c->tmp4, c->perm, 0, n, reinterpret_cast<double4*>(d_accel4), c->stream);
-    c->force = saved_force; c->have_accel = false; c->uploaded = true;
-    if (rc) { cudaEventDestroy(ev); return rc; }
+    c->force = saved_force;
+    if (rc) return rc;
     c->launches += 2;
-    if (user) { NB_CUDA(cudaEventRecord(ev, c->stream)); NB_CUDA(cudaStreamWaitEvent(user, ev, 0)); }
+    if (user) { NB_CUDA(cudaEventRecord(c->ev_user, c->stream)); NB_CUDA(cudaStreamWaitEvent(user, c->ev_user, 0)); }
     else NB_CUDA(cudaStreamSynchronize(c->stream));
-    NB_CUDA(cudaEventDestroy(ev));
     return NB_OK;
 }
 
