@@ -117,6 +117,15 @@ def reference_cuda_bar(n):
         return {"unavailable": str(e)[:200]}
 
 
+def host_cores(eng):
+    """Threads for the CPU arm: every core this process may run on. omp_get_max_threads() is not used alone because
+    torchrun exports OMP_NUM_THREADS=1 to its workers, which would silently turn the OpenMP reference into a serial run."""
+    try:
+        return max(len(os.sched_getaffinity(0)), 1)
+    except AttributeError:
+        return max(os.cpu_count() or 1, eng.max_threads())
+
+
 def pinned(n_rows):
     import torch
     t = torch.empty((n_rows, 4), dtype=torch.float64).pin_memory()
@@ -129,7 +138,7 @@ def cpu_baseline(workload_n, steps=1, kind_pref="reference"):
     ref = nbtest.Ref.try_load() if kind_pref == "reference" else None
     eng = ref if ref is not None else nbtest.Oracle()
     kind = "reference" if ref is not None else "port"
-    cores = eng.max_threads()
+    cores = host_cores(eng)
     eng.set_threads(cores)
     # sample size: ~10-30 s of CPU work. One VV step = 2 force evaluations = 2 n^2 interactions at ~0.27 Gint/s/core.
     n_s = 16384
@@ -157,7 +166,7 @@ def run_reference_arm(args, rank, world):
     ref = nbtest.Ref.try_load()
     eng = ref if ref is not None else nbtest.Oracle()
     kind = "reference" if ref is not None else "port"
-    cores = eng.max_threads(); eng.set_threads(cores)
+    cores = host_cores(eng); eng.set_threads(cores)
     n_s = args.ref_n
     pm, v = nbtest.gen_spiral(n_s, seed=42)
     run = (lambda: eng.run(pm, v, nbtest.VV, nbtest.PAIRWISE, 0.04, 1)) if ref is not None else \
