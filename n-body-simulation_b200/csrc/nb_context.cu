@@ -159,18 +159,19 @@ int check_force_method(int force) {
 
 int splits_for(nb_ctx* c, int iblocks, int jcount) {
     if (c->j_splits > 0) return c->j_splits < jcount ? c->j_splits : jcount;
-    // All CTAs of a launch do the same amount of work (jcount / S tiles for 512 i-particles), so the launch runs in
-    // ceil(CTAs / slots) waves of sm_count SMs (148 on B200) x 2 resident CTAs. Pick the S whose last wave is fullest,
-    // among those that give at least ~4 waves; ties go to the smaller S (less partial-sum traffic).
-    const double slots = (double)c->sm_count * 2.0;
-    int best = 1; double best_eff = -1.0;
-    for (int S = 1; S <= 32 && S <= jcount; ++S) {
-        const double waves = (double)iblocks * S / slots;
-        double eff = waves / (double)(long)(waves + 0.999999);
-        if (waves < 4.0) eff *= 0.5 + waves / 8.0;          // too few waves: prologue/tail dominate, keep splitting
-        if (eff > best_eff * 1.015) { best_eff = eff; best = S; }
-    }
-    return best;
+    // CTAs of one launch differ a lot in cost (refined tiles, FP64 hand-offs, Hilbert-curve jumps), so the j-range is cut
+    // much finer than the sm_count x 2 resident-CTA slots need and the block scheduler does the balancing: measured
+    // (profiles/r01_kappa_splits_sweep.json) 64 splits beat the wave-filling choice by 6 % at N = 65536, 4.5 % at 262144
+    // and 1.2 % at 1M. Aim for ~128 CTAs per slot, at least 4 j-tiles per CTA, at most 64 splits, and keep the
+    // partial-sum slots (3 x npad doubles each) under 8 GB.
+    const long slots = (long)c->sm_count * 2;
+    long S = (128 * slots + iblocks - 1) / (iblocks > 0 ? iblocks : 1);
+    if (S > 64) S = 64;
+    if (S > jcount / 4) S = jcount / 4;
+    const long per_slot = 3L * c->npad * (long)sizeof(double);
+    const long mem_cap = (8L << 30) / per_slot / 3;        // far A + far B + near may each take this many
+    if (S > mem_cap) S = mem_cap;
+    return S < 1 ? 1 : (int)S;
 }
 
 int ensure_part(nb_ctx* c, int S_total) {
