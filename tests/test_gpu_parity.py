@@ -389,3 +389,23 @@ def test_symmetries_at_full_size(lib, n, prec):
     # 4. Newton's third law
     tot = (pm[:, 3:4] * a0[:, :3]).sum(0); scale = np.abs(pm[:, 3:4] * a0[:, :3]).sum(0)
     assert np.all(np.abs(tot) <= (2e-6 if prec == FP32 else 1e-12) * scale)
+
+
+@pytest.mark.skipif(os.environ.get("NB_TEST_16M") != "1",
+                    reason="C5 (N = 16,777,216) takes ~2.5 min of GPU time per evaluation pair: set NB_TEST_16M=1 to run it "
+                           "(last run recorded in profiles/r01_c5_16M_parity.txt)")
+def test_c5_spiral_16M_sampled_arbiter(lib, oracle):
+    """BASELINE.json's largest configuration on one GPU: 2.8e14 pair interactions per evaluation. Checked through the
+    sampled-subset arbiter (96 particles against all 16.7M in long double on the CPU), finiteness and Newton's third law."""
+    n = 16777216
+    pm, v = nbtest.gen_spiral(n, seed=42)
+    a = gpu_accel(lib, pm, v, PAIRWISE, FP32)
+    assert np.all(np.isfinite(a))
+    idx = np.random.default_rng(0).choice(n, 96, replace=False)
+    idx[:3] = [0, 1, n - 1]
+    err = nbtest.rel_err(a[idx], oracle.forces_subset(pm, PAIRWISE, idx))
+    print(f"C5 N={n}: sampled arbiter max rel err {err.max():.3e}, median {np.median(err):.3e}")
+    assert err.max() <= TOL[FP32]
+    tot = (pm[:, 3:4] * a[:, :3]).sum(0); scale = np.abs(pm[:, 3:4] * a[:, :3]).sum(0)
+    print(f"C5 sum m a / sum |m a| = {np.abs(tot / scale).max():.3e}")
+    assert np.all(np.abs(tot) <= 2e-6 * scale)
