@@ -166,6 +166,22 @@ int nb_run_simulation(long n, double* posMass4, double* vel4, int integration_me
                       double* h_particleData, double* h_systemData, double* h_staticData, long num_time_steps,
                       int precision, int subtract_com, int device);
 
+/* runVisualizationOnGPU(particles, method, forceMethod, dt, steps, stepFreq, physicsStepsPerFrame)
+ * (visualization/cuda/VisualizationKernels.cu:52-300) without a window: the same loop — initial force, then per frame
+ * physics_steps_per_frame integrator steps (<= 0: 1, as the reference) followed by one image of the state — with the
+ * frame rendered by nb_render's CUDA kernels (reference camera defaults, VELOCITY_MAGNITUDE colours, 30 px points,
+ * max-speed moving average across frames) instead of OpenGL, which is unavailable on the target machine.
+ * scale > 0: world-to-view factor (the reference's GPU driver uses 1e-3, VisualizationUtils.cpp:19); scale <= 0:
+ * 2 / max |r| of the initial state, kept for the whole run (the reference's CPU viewer, core/System.cpp:236-248).
+ * frame_dir != NULL: every frame_stride-th frame (<= 0: 1) is written as binary PPM frame_dir/frame_NNNNNN.ppm (the
+ * directory must exist); NULL: frames are rendered and dropped. last_rgba8 (may be NULL): width*height*4 bytes, receives
+ * the last frame. frames2 (may be NULL) receives (frames rendered, frames written). The final state is written back into
+ * posMass4 / vel4 like the reference does (:259-261). */
+int nb_run_visualization(long n, double* posMass4, double* vel4, int integration_method, int force_method,
+                         double dt, int steps, int physics_steps_per_frame, int width, int height, float scale,
+                         const char* frame_dir, int frame_stride, unsigned char* last_rgba8, long* frames2,
+                         int precision, int subtract_com, int device);
+
 /* ---- device-pointer entry points: the inner boundary of the reference drivers ------------------------------------ */
 /* launchForceKernel(method, blocks, blockSize, smem, stream, d_posMass, d_accel, avgMass, n)
  * (cuda/ForceKernels.cu:208-232). d_posMass4 / d_accel4 are caller-owned device double4 arrays; the context provides

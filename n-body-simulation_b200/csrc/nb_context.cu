@@ -7,6 +7,7 @@
 #include "nb_common.cuh"
 
 #include <cstdarg>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
@@ -753,6 +754,54 @@ int nb_run_simulation(long n, double* posMass4, double* vel4, int integ, int for
         }
     }
     if (!rc) rc = nb_download(c, posMass4, vel4);                                          // :246-249
+    nb_destroy(c);
+    return rc;
+}
+
+int nb_run_visualization(long n, double* posMass4, double* vel4, int integ, int force, double dt, int steps,
+                         int physics_steps_per_frame, int width, int height, float scale, const char* frame_dir,
+                         int frame_stride, unsigned char* last_rgba8, long* frames2, int precision, int subtract_com, int device) {
+    if (width <= 0 || height <= 0 || width > 16384 || height > 16384)
+        return fail(NB_ERR_INVALID, "nb_run_visualization: image %d x %d", width, height);
+    if (steps < 0) return fail(NB_ERR_INVALID, "nb_run_visualization: steps=%d", steps);
+    const int per_frame = physics_steps_per_frame > 0 ? physics_steps_per_frame : 1;     // VisualizationKernels.cu:159-160
+    const int stride = frame_stride > 0 ? frame_stride : 1;
+    std::vector<unsigned char> img((size_t)width * height * 4);
+    nb_ctx* c = nullptr;
+    int rc = nb_create(&c, n, device, precision); if (rc) return rc;
+    rc = nb_set_methods(c, integ, force, subtract_com);
+    if (!rc) rc = nb_upload(c, posMass4, vel4);
+    if (!rc) rc = nb_compute_accel(c);                                                   // :118-133
+    long rendered = 0, written = 0;
+    int done = 0;
+    while (!rc && done < steps) {                                                        // :163-250
+        const int k = steps - done < per_frame ? steps - done : per_frame;
+        rc = nb_step(c, dt, k);
+        done += k;
+        float info[4] = {0.f, 0.f, 0.f, 0.f};
+        if (!rc) rc = nb_render(c, width, height, 0.2f, 0.9f, 5.0f, 0.0f, 0.0f, scale, 30.0f, 1, nullptr, nullptr, img.data(), info);
+        if (rc) break;
+        if (scale <= 0.f) scale = info[3];              // the scale found for the first frame stays for the run
+        if (frame_dir && rendered % stride == 0) {
+            char path[4096];
+            snprintf(path, sizeof(path), "%s/frame_%06ld.ppm", frame_dir, written);
+            FILE* f = fopen(path, "wb");
+            if (!f) { rc = fail(NB_ERR_INVALID, "nb_run_visualization: cannot write %s", path); break; }
+            fprintf(f, "P6\n%d %d\n255\n", width, height);
+            std::vector<unsigned char> row((size_t)width * 3);
+            for (int y = 0; y < height; ++y) {
+                const unsigned char* src = img.data() + (size_t)y * width * 4;
+                for (int x = 0; x < width; ++x) { row[3 * x] = src[4 * x]; row[3 * x + 1] = src[4 * x + 1]; row[3 * x + 2] = src[4 * x + 2]; }
+                fwrite(row.data(), 1, row.size(), f);
+            }
+            fclose(f);
+            ++written;
+        }
+        ++rendered;
+    }
+    if (!rc) rc = nb_download(c, posMass4, vel4);                                         // :259-261
+    if (!rc && last_rgba8 && rendered > 0) memcpy(last_rgba8, img.data(), img.size());
+    if (frames2) { frames2[0] = rendered; frames2[1] = written; }
     nb_destroy(c);
     return rc;
 }

@@ -66,6 +66,9 @@ int main(int argc, char** argv) {
         const nbh::RunReport rep = nbh::run_config(cfg, false);
         const double n2 = (double)rep.n * (double)rep.n;
         std::cout << "\nSimulation time: " << rep.run_seconds << " seconds (using GPU)" << std::endl;   // main.cpp:617-627
+        if (rep.frames_rendered > 0)
+            std::cout << "Frames: " << rep.frames_rendered << " rendered, " << rep.frames_written << " written to " << rep.output_path
+                      << " (" << rep.frames_rendered / rep.run_seconds << " FPS)" << std::endl;    // VisualizationKernels.cu:287-291
         if (rep.run_seconds > 0 && rep.steps > 0)
             std::cout << "Throughput: " << rep.steps / rep.run_seconds << " steps/s, "
                       << n2 * (double)(rep.steps + 1) / rep.run_seconds / 1e9 << " G-interactions/s (N=" << rep.n << ", "

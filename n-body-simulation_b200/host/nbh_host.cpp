@@ -5,6 +5,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdint>
+#include <filesystem>
 #include <fstream>
 #include <iomanip>
 #include <iostream>
@@ -54,6 +55,16 @@ Config parse_config_text(const std::string& text) {
     if (j.contains("subtractCom")) c.subtractCom = j["subtractCom"].as_bool();
     if (j.contains("device")) c.device = j["device"].as_int();
     if (j.contains("snapshotOut")) c.snapshotOut = j["snapshotOut"].as_string();
+    if (j.contains("frames")) {
+        const Json& f = j["frames"];
+        c.hasFrames = true;
+        if (f.contains("dir")) c.frameDir = f["dir"].as_string();
+        if (f.contains("width")) c.frameWidth = f["width"].as_int();
+        if (f.contains("height")) c.frameHeight = f["height"].as_int();
+        if (f.contains("physicsStepsPerFrame")) c.physicsStepsPerFrame = f["physicsStepsPerFrame"].as_int();
+        if (f.contains("every")) c.frameEvery = f["every"].as_int();
+        if (f.contains("scale")) c.frameScale = f["scale"].as_double();
+    }
     return c;
 }
 
@@ -348,8 +359,9 @@ RunReport run_config(const Config& cfg, bool quiet) {
     RunReport rep;
     if (cfg.executionMode != ExecutionMode::GPU)
         throw std::runtime_error("executionMode \"CPU\" is the reference's OpenMP path; this host drives the B200 library only (no CPU fallback)");
-    if (cfg.outputMode == OutputMode::VISUALIZATION)
-        throw std::runtime_error("outputMode \"VISUALIZATION\" is reference-only: no graphics stack on this machine");
+    if (cfg.outputMode == OutputMode::VISUALIZATION && !cfg.hasFrames)
+        throw std::runtime_error("outputMode \"VISUALIZATION\": the interactive OpenGL viewer is reference-only (no graphics stack on "
+                                 "this machine); add a \"frames\" object to the config for headless PPM frames of the same shader arithmetic");
     const long steps = (long)(cfg.years / cfg.dtYears);                 // main.cpp:496
     const long stepFreq = std::max(1L, steps / 500);                    // main.cpp:499,525
     auto t0 = std::chrono::high_resolution_clock::now();
@@ -372,6 +384,17 @@ RunReport run_config(const Config& cfg, bool quiet) {
     if (cfg.outputMode == OutputMode::BENCHMARK) {
         check(nb_run_benchmark((long)p.n, p.posMass.data(), p.vel.data(), (int)cfg.integrationMethod, (int)cfg.forceMethod,
                                cfg.dtYears, (int)steps, 256, prec, cfg.subtractCom ? 1 : 0, cfg.device));
+    } else if (cfg.outputMode == OutputMode::VISUALIZATION) {
+        // runVisualizationOnGPU (visualization/cuda/VisualizationKernels.cu:52-300) without the window
+        const std::string dir = cfg.outputDir + cfg.frameDir;
+        std::filesystem::create_directories(dir);
+        long frames[2] = {0, 0};
+        if (!quiet) std::cout << "Starting headless visualization with " << p.n << " particles, frames -> " << dir << std::endl;
+        check(nb_run_visualization((long)p.n, p.posMass.data(), p.vel.data(), (int)cfg.integrationMethod, (int)cfg.forceMethod,
+                                   cfg.dtYears, (int)steps, cfg.physicsStepsPerFrame, cfg.frameWidth, cfg.frameHeight,
+                                   (float)cfg.frameScale, dir.c_str(), cfg.frameEvery > 0 ? cfg.frameEvery : (int)stepFreq, nullptr,
+                                   frames, prec, cfg.subtractCom ? 1 : 0, cfg.device));
+        rep.frames_rendered = frames[0]; rep.frames_written = frames[1]; rep.output_path = dir;
     } else {
         const size_t T = (size_t)(steps / stepFreq + 1);                // core/System.cpp:107
         std::vector<double> pd(T * p.n * 6, 0.0), sd(T * 2, 0.0), st(p.n * 2, 0.0);

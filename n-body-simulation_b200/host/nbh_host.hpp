@@ -6,6 +6,10 @@
 //     "precision": "FP32" | "FP64"   (default FP32 for BENCHMARK, FP64 for FILE_CSV)
 //     "subtractCom": true | false    (default true: the reference CPU integrators' behaviour)
 //     "device": integer
+//     "frames": {"dir": "frames", "width": 1280, "height": 720, "physicsStepsPerFrame": 1, "scale": 0, "every": 0}
+//                                    — with outputMode "VISUALIZATION": headless PPM frames (the viewer's shader arithmetic
+//                                      as CUDA kernels) instead of the reference's OpenGL window; "every" = write every
+//                                      k-th rendered frame (0: the reference's print frequency max(1, steps/500))
 //     "snapshotOut": "path.nbin"     — write the final state as a binary snapshot (checkpoint); a "FROM_FILE" filePath
 //                                      ending in ".nbin" reads one back (resume; partialCount <= 0 means all particles)
 #pragma once
@@ -53,6 +57,8 @@ struct Config {
     bool subtractCom = true;
     int device = -1;
     std::string snapshotOut;
+    bool hasFrames = false; std::string frameDir = "frames"; int frameWidth = 1280, frameHeight = 720;   // VisualizationUtils.cpp:15-16
+    int physicsStepsPerFrame = 0, frameEvery = 0; double frameScale = 0.0;
 };
 
 Config parse_config_text(const std::string& text);
@@ -82,7 +88,7 @@ bool write_csv(const std::string& filename, const std::string& metadata, size_t 
                const double* particleData6, const double* systemData2, const double* staticData2);
 
 // Run a parsed configuration through the C ABI. Returns 0 on success; throws std::runtime_error on library errors.
-struct RunReport { double init_seconds = 0, run_seconds = 0; long steps = 0; size_t n = 0; std::string output_path; };
+struct RunReport { double init_seconds = 0, run_seconds = 0; long steps = 0; size_t n = 0; std::string output_path; long frames_rendered = 0, frames_written = 0; };
 RunReport run_config(const Config& cfg, bool quiet);
 
 // --auto-benchmark harness (core/main.cpp:13-452): size sweep x repeated runs on random initial conditions -> statistics

@@ -5,6 +5,7 @@
 #include "System.hpp"
 #include "nbody_b200.h"
 
+#include <cstdio>
 #include <cstdlib>
 #include <stdexcept>
 
@@ -24,7 +25,18 @@ extern "C" void runSimulationOnGPU(Particles& p, IntegrationMethod m, ForceMetho
                             stepFreq, out.h_particleData, out.h_systemData, out.h_staticData, (long)out.numTimeSteps,
                             env_int("NB_PRECISION", NB_PREC_FP64), env_int("NB_SUBTRACT_COM", 1), -1));
 }
-// visualization/cuda/VisualizationKernels.cu:52-303 — needs OpenGL: unavailable on this box.
-extern "C" void runVisualizationOnGPU(Particles&, IntegrationMethod, ForceMethod, double, int, double, int) {
-    throw std::runtime_error("VISUALIZATION is reference-only (no graphics stack on the target machine)");
+// visualization/cuda/VisualizationKernels.cu:52-303 — the reference opens an OpenGL window: unavailable on this box. With
+// NB_FRAME_DIR set, the same loop runs headless and every stepFreq-th frame lands there as a PPM (nb_run_visualization);
+// without it the call fails the way the reference's main already handles (core/main.cpp:597-615).
+extern "C" void runVisualizationOnGPU(Particles& p, IntegrationMethod m, ForceMethod f, double dt, int steps, double stepFreq,
+                                      int physicsStepsPerFrame) {
+    const char* dir = std::getenv("NB_FRAME_DIR");
+    if (!dir) throw std::runtime_error("VISUALIZATION is reference-only (no graphics stack on the target machine); "
+                                       "set NB_FRAME_DIR for headless PPM frames");
+    long frames[2] = {0, 0};
+    check(nb_run_visualization((long)p.n, &p.posMass[0].x, &p.vel[0].x, static_cast<int>(m), static_cast<int>(f), dt, steps,
+                               physicsStepsPerFrame, env_int("NB_FRAME_WIDTH", 1280), env_int("NB_FRAME_HEIGHT", 720), 0.0f, dir,
+                               stepFreq >= 1.0 ? (int)stepFreq : 1, nullptr, frames, env_int("NB_PRECISION", NB_PREC_FP32),
+                               env_int("NB_SUBTRACT_COM", 1), -1));
+    std::printf("Headless visualization: %ld frames rendered, %ld written to %s\n", frames[0], frames[1], dir);
 }

@@ -33,6 +33,11 @@ int main(int argc, char** argv) {
             dvel = std::fmax(dvel, std::fmax(std::fabs(a.vel[i].x - b.vel[i].x), std::fmax(std::fabs(a.vel[i].y - b.vel[i].y), std::fabs(a.vel[i].z - b.vel[i].z))));
         }
         const double ec = cpu.computeTotalEnergy(), eg = gpu.computeTotalEnergy();
+        if (std::getenv("NB_FRAME_DIR")) {     // the reference's VISUALIZATION dispatch (System.cpp:96-99,210-214,367-382) on the headless shim
+            Particles vizCopy(init.particles);
+            System viz(std::move(vizCopy), integ, force, ExecutionMode::GPU, OutputMode::VISUALIZATION);
+            viz.runSimulation(dt, steps, 2.0, "", "");
+        }
         std::printf("{\"n\": %zu, \"steps\": %d, \"max_abs_dpos\": %.3e, \"max_abs_dvel\": %.3e, \"E0\": %.15e, \"E_cpu\": %.15e, \"E_gpu\": %.15e}\n",
                     a.n, steps, dpos, dvel, e0, ec, eg);
         return 0;

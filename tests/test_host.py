@@ -232,6 +232,39 @@ def test_auto_benchmark_sweep_on_gpu(tmp_path):
 
 
 @pytest.mark.gpu
+def test_host_visualization_mode_writes_headless_frames(tmp_path, host):
+    """outputMode VISUALIZATION + a "frames" block: the reference's render loop (VisualizationKernels.cu:52-300) without a
+    window. 12 steps, one step per frame, every 4th frame written -> 12 rendered, 3 PPM files; the state advances exactly
+    as in BENCHMARK mode."""
+    frames = {"dir": "frames", "width": 320, "height": 180, "physicsStepsPerFrame": 1, "every": 4}
+    text = cfg_text(seed=3, years=0.5, dtYears=0.04, outputMode="VISUALIZATION", frames=frames, snapshotOut="viz.nbin",
+                    precision="FP64")
+    (tmp_path / "config.json").write_text(text)
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert "Frames: 12 rendered, 3 written" in r.stdout
+    files = sorted(os.listdir(tmp_path / "frames"))
+    assert files == ["frame_000000.ppm", "frame_000001.ppm", "frame_000002.ppm"]
+    imgs = []
+    for f in files:
+        raw = (tmp_path / "frames" / f).read_bytes()
+        assert raw.startswith(b"P6\n320 180\n255\n") and len(raw) == len(b"P6\n320 180\n255\n") + 320 * 180 * 3
+        imgs.append(np.frombuffer(raw[-320 * 180 * 3:], dtype=np.uint8).reshape(180, 320, 3))
+    background = np.array([5, 5, 13], dtype=np.uint8)                    # clear colour (0.02, 0.02, 0.05) quantised
+    lit = [(im != background).any(axis=2).sum() for im in imgs]
+    assert min(lit) > 600                                               # 600 particles with 30 px sprites: thousands of pixels
+    assert not np.array_equal(imgs[0], imgs[2])                         # the particles move between frames
+    (tmp_path / "config.json").write_text(cfg_text(seed=3, years=0.5, dtYears=0.04, snapshotOut="bench.nbin", precision="FP64"))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    assert (tmp_path / "viz.nbin").read_bytes() == (tmp_path / "bench.nbin").read_bytes()
+    # without the "frames" block the mode stays a clean error
+    (tmp_path / "config.json").write_text(cfg_text(seed=3, outputMode="VISUALIZATION"))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 1 and "reference-only" in r.stderr and "frames" in r.stderr
+
+
+@pytest.mark.gpu
 def test_host_file_csv_mode(tmp_path, host, oracle):
     text = cfg_text(seed=2, years=1.0, dtYears=0.01, outputMode="FILE_CSV", forceMethod="ADAPTIVE_MUTUAL")
     text = text.replace('"nParticles": 600', '"nParticles": 40')
