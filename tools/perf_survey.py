@@ -19,6 +19,7 @@ CASES = [
     ("   spiral 262144 PAIRWISE fp32", lambda: nbtest.gen_spiral(262144, seed=42), nbtest.PAIRWISE, nbtest.FP32, 5),
     ("C3 spiral 1048576 PAIRWISE fp32", lambda: nbtest.gen_spiral(1048576, seed=42), nbtest.PAIRWISE, nbtest.FP32, 3),
     ("   spiral 1048576 ADAPTIVE fp32", lambda: nbtest.gen_spiral(1048576, seed=42), nbtest.ADAPTIVE, nbtest.FP32, 3),
+    ("   spiral 1048576 PAIRWISE_AVX2_FP32 (Plummer) fp32", lambda: nbtest.gen_spiral(1048576, seed=42), nbtest.AVX2, nbtest.FP32, 3),
 ]
 if len(sys.argv) > 1 and sys.argv[1] == "quick":
     CASES = CASES[:3]
