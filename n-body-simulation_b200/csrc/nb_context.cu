@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 #include <dlfcn.h>
 #include <vector>
 
@@ -72,6 +73,7 @@ struct nb_ctx {
     static constexpr int kRing = 64;
     cudaEvent_t fev0[kRing] = {}, fev1[kRing] = {};   // ring of force-evaluation event pairs
     long fev_count = 0;
+    char* slab = nullptr; size_t slab_bytes = 0;      // one allocation behind all npad-sized arrays (alloc_arrays)
     double4 *pos = nullptr, *vel = nullptr, *tmp4 = nullptr, *stage_pos = nullptr, *stage_vel = nullptr;
     unsigned int* perm = nullptr;          // perm[sorted slot] = caller index
     double* snap = nullptr;                // snapshot staging [n][6] + [n][2], allocated by the first nb_snapshot
@@ -94,10 +96,8 @@ struct nb_ctx {
 namespace {
 
 void free_arrays(nb_ctx* c) {
-    cudaFree(c->pos); cudaFree(c->vel); cudaFree(c->tmp4); cudaFree(c->stage_pos); cudaFree(c->stage_vel);
-    cudaFree(c->acc); cudaFree(c->part); cudaFree(c->red_part); cudaFree(c->pk); cudaFree(c->perm); cudaFree(c->perm2); cudaFree(c->snap);
-    cudaFree(c->ss.keys_in); cudaFree(c->ss.keys_out); cudaFree(c->ss.idx_in); cudaFree(c->ss.extent_part);
-    cudaFree(c->ss.box); cudaFree(c->ss.cub_temp);
+    cudaFree(c->slab); c->slab = nullptr; c->slab_bytes = 0;            // every npad-sized array lives in this one block
+    cudaFree(c->part); cudaFree(c->snap);
     cudaFree(c->stats); c->stats = nullptr; c->collect_stats = 0;       // sized by npad as well
     c->pos = c->vel = c->tmp4 = c->stage_pos = c->stage_vel = nullptr;
     c->acc = c->part = c->red_part = c->snap = nullptr; c->pk = nullptr; c->perm = nullptr; c->perm2 = nullptr; c->part_bytes = 0;
@@ -106,28 +106,34 @@ void free_arrays(nb_ctx* c) {
 }
 
 // Everything whose size depends on npad (the padded particle count).
+// One cudaMalloc for all of it: a context is created and destroyed inside every nb_run_benchmark / nb_run_simulation
+// call (the reference's per-call life cycle), and ~18 separate cudaMalloc / cudaFree pairs were 8 of the 15 ms that cost.
 int alloc_arrays(nb_ctx* c) {
     const size_t np = (size_t)c->npad, n = (size_t)c->n;
-    NB_CUDA(cudaMalloc(&c->pos, np * sizeof(double4)));
-    NB_CUDA(cudaMalloc(&c->vel, np * sizeof(double4)));
-    NB_CUDA(cudaMalloc(&c->tmp4, np * sizeof(double4)));
-    NB_CUDA(cudaMalloc(&c->stage_pos, n * sizeof(double4)));
-    NB_CUDA(cudaMalloc(&c->stage_vel, n * sizeof(double4)));
-    NB_CUDA(cudaMalloc(&c->acc, np * 3 * sizeof(double)));
-    NB_CUDA(cudaMalloc(&c->red_part, (np / kThreads) * 4 * sizeof(double)));
-    NB_CUDA(cudaMalloc(&c->perm, np * sizeof(unsigned int)));
-    NB_CUDA(cudaMalloc(&c->perm2, np * sizeof(unsigned int)));
-    NB_CUDA(cudaMalloc(&c->ss.keys_in, n * sizeof(unsigned long long)));
-    NB_CUDA(cudaMalloc(&c->ss.keys_out, n * sizeof(unsigned long long)));
-    NB_CUDA(cudaMalloc(&c->ss.idx_in, n * sizeof(unsigned int)));
-    NB_CUDA(cudaMalloc(&c->ss.extent_part, (np / kThreads) * 6 * sizeof(double)));
-    NB_CUDA(cudaMalloc(&c->ss.box, 8 * sizeof(double)));
     c->ss.cub_bytes = sort_temp_bytes((long)n);
-    NB_CUDA(cudaMalloc(&c->ss.cub_temp, c->ss.cub_bytes ? c->ss.cub_bytes : 16));
-    if (c->precision == NB_PREC_FP32) {
-        NB_CUDA(cudaMalloc(&c->pk, np * kNC * sizeof(float)));
-        NB_CUDA(cudaMemsetAsync(c->pk, 0, np * kNC * sizeof(float), c->stream));
-    }
+    char* base = nullptr;
+    size_t off = 0;
+    auto carve = [&](auto*& ptr, size_t count) {
+        using T = std::remove_reference_t<decltype(*ptr)>;
+        ptr = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += (count * sizeof(T) + 255) / 256 * 256;
+    };
+    auto layout = [&]() {
+        off = 0;
+        carve(c->pos, np); carve(c->vel, np); carve(c->tmp4, np); carve(c->stage_pos, n); carve(c->stage_vel, n);
+        carve(c->acc, np * 3); carve(c->red_part, (np / kThreads) * 4);
+        carve(c->perm, np); carve(c->perm2, np);
+        carve(c->ss.keys_in, n); carve(c->ss.keys_out, n); carve(c->ss.idx_in, n);
+        carve(c->ss.extent_part, (np / kThreads) * 6); carve(c->ss.box, 8);
+        unsigned char* cub = nullptr; carve(cub, c->ss.cub_bytes ? c->ss.cub_bytes : 16); c->ss.cub_temp = cub;
+        if (c->precision == NB_PREC_FP32) carve(c->pk, np * kNC); else c->pk = nullptr;
+    };
+    layout();                                   // sizes only
+    c->slab_bytes = off;
+    NB_CUDA(cudaMalloc(&c->slab, c->slab_bytes));
+    base = c->slab;
+    layout();                                   // pointers
+    if (c->pk) NB_CUDA(cudaMemsetAsync(c->pk, 0, np * kNC * sizeof(float), c->stream));
     NB_CUDA(cudaMemsetAsync(c->pos, 0, np * sizeof(double4), c->stream));
     NB_CUDA(cudaMemsetAsync(c->vel, 0, np * sizeof(double4), c->stream));
     NB_CUDA(cudaMemsetAsync(c->acc, 0, np * 3 * sizeof(double), c->stream));
@@ -371,11 +377,14 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
     if (device < 0) { NB_CUDA(cudaGetDevice(&device)); }
     if (device >= ndev) return fail(NB_ERR_INVALID, "nb_create: device %d of %d", device, ndev);
     NB_CUDA(cudaSetDevice(device));
-    cudaDeviceProp prop; NB_CUDA(cudaGetDeviceProperties(&prop, device));
-    if (prop.major != 10) return fail(NB_ERR_NO_DEVICE, "device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
+    int cc_major = 0, cc_minor = 0, sm_count = 0;      // three attribute queries: cudaGetDeviceProperties costs milliseconds per call
+    NB_CUDA(cudaDeviceGetAttribute(&cc_major, cudaDevAttrComputeCapabilityMajor, device));
+    NB_CUDA(cudaDeviceGetAttribute(&cc_minor, cudaDevAttrComputeCapabilityMinor, device));
+    NB_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, device));
+    if (cc_major != 10) return fail(NB_ERR_NO_DEVICE, "device %d is sm_%d%d; this library contains sm_100a code only", device, cc_major, cc_minor);
     nb_ctx* c = new nb_ctx();
     c->device = device; c->precision = precision; c->n = n;
-    if (prop.multiProcessorCount > 0) c->sm_count = prop.multiProcessorCount;
+    if (sm_count > 0) c->sm_count = sm_count;
     c->npad = round_up(n, kAlign); c->ntiles = (int)(c->npad / kTJ);
     c->i0 = 0; c->ni = c->npad;
     auto bail = [&](int rc) { nb_destroy(c); return rc; };
