@@ -81,4 +81,9 @@ int nbh_run_sweep(const int* sizes, long count, int force, int integ, int runs, 
                        for (const auto& r : res) if (!r.success) throw std::runtime_error(r.errorMessage);
                        return 0; });
 }
+// FILE_CSV sink on caller-provided arrays (output/OutputUtils.cpp:8-59).
+int nbh_write_csv(const char* filename, const char* metadata, long n, long T, const double* particleData6,
+                  const double* systemData2, const double* staticData2) {
+    return guard([&] { return nbh::write_csv(filename, metadata, (size_t)n, (size_t)T, particleData6, systemData2, staticData2) ? 0 : 1; });
+}
 }

@@ -13,6 +13,8 @@
 //   Initializer::init*              simulator/core/Initializer.cpp:17-53,71-154,168-239,360-469
 #include "System.hpp"
 #include "Initializer.hpp"
+#include "OutputData.hpp"
+#include "OutputUtils.hpp"
 #include <omp.h>
 #include <cstring>
 #include <cstdio>
@@ -109,4 +111,15 @@ int nbref_init_file(const char* path, int count, long cap, long* n_out, double* 
           export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
 }
 
+// The reference's FILE_CSV sink (output/OutputUtils.cpp:8-59) on caller-provided OutputData contents: fixture for the
+// byte-for-byte comparison with the host's writer.
+int nbref_write_csv(const char* filename, const char* metadata, long n, long T, const double* particleData6,
+                    const double* systemData2, const double* staticData2) {
+    OutputData out((size_t)n, (size_t)T, ExecutionMode::CPU);
+    std::memcpy(out.h_particleData, particleData6, (size_t)n * T * 6 * sizeof(double));
+    std::memcpy(out.h_systemData, systemData2, (size_t)T * 2 * sizeof(double));
+    std::memcpy(out.h_staticData, staticData2, (size_t)n * 2 * sizeof(double));
+    flushCSVOutput(out, filename, metadata);
+    return 0;
+}
 } // extern "C"

@@ -144,6 +144,28 @@ def test_host_generators_match_reference_distributions(host, ref):
     assert abs(np.abs(v[:, :3]).mean() - np.abs(rv[:, :3]).mean()) < 0.1
 
 
+def test_csv_sink_is_byte_identical_to_the_reference_writer(host, ref, tmp_path):
+    """FILE_CSV text (metadata, header, fixed 8-digit fields, 15-digit energy): the host's writer against the reference's own
+    flushCSVOutput (output/OutputUtils.cpp:8-59, compiled unmodified into oracle/_ref) on the same OutputData contents."""
+    rng = np.random.default_rng(12)
+    n, T = 37, 5
+    pd = rng.normal(0, 1, (T, n, 6)) * 10.0 ** rng.integers(-9, 7, (T, n, 6))        # tiny, huge, negative values
+    pd[0, 0] = [0.0, -0.0, 1e-9, -4.9999999949e-9, 123456789.123456789, -1.0]         # rounding edges of %.8f
+    sd = np.stack([np.arange(T) * 0.04, rng.normal(-4e-3, 1e-3, T)], axis=1)
+    st = np.stack([np.arange(n, dtype=float), 10.0 ** rng.uniform(-10, 6, n)], axis=1)
+    meta = "# years: 100.000000\n# Random particles\n# dt (years): 0.040000\n"
+    args = [C.c_char_p, C.c_char_p, C.c_long, C.c_long, nbtest._dp, nbtest._dp, nbtest._dp]
+    host.nbh_write_csv.argtypes = args
+    ref.l.nbref_write_csv.argtypes = args
+    a, b = tmp_path / "host.csv", tmp_path / "ref.csv"
+    pdc, sdc, stc = (np.ascontiguousarray(x) for x in (pd, sd, st))
+    assert host.nbh_write_csv(str(a).encode(), meta.encode(), n, T, nbtest._p(pdc), nbtest._p(sdc), nbtest._p(stc)) == 0
+    assert ref.l.nbref_write_csv(str(b).encode(), meta.encode(), n, T, nbtest._p(pdc), nbtest._p(sdc), nbtest._p(stc)) == 0
+    ta, tb = a.read_bytes(), b.read_bytes()
+    assert len(ta.splitlines()) == 3 + 1 + 1 + n * T
+    assert ta == tb
+
+
 def test_host_binary_fails_loudly_without_gpu(tmp_path, lib):
     if lib.l.nb_device_count() > 0:
         pytest.skip("a GPU is present")
