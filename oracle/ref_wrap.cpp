@@ -87,28 +87,34 @@ double nbref_energy(long n, const double* posMass4, const double* vel4) {
     return sys.computeTotalEnergy();
 }
 
+static std::string g_last_metadata;
+// Metadata text of the last nbref_init_* call (what the reference prepends to its CSV files).
+long nbref_last_metadata(char* buf, long cap) {
+    if (buf && cap > 0) { std::strncpy(buf, g_last_metadata.c_str(), (size_t)cap - 1); buf[cap - 1] = 0; }
+    return (long)g_last_metadata.size();
+}
 // Reference generators (seeded from std::random_device inside the reference: NOT reproducible; used for
 // statistical comparison with the seeded generators and as CPU-baseline workloads).
 int nbref_init_random(int n, double minMass, double maxMass, double L, double maxVel, double minDist,
                       long cap, long* n_out, double* posMass4, double* vel4) {
     try { InitResult r = Initializer::initRandomParticles(n, minMass, maxMass, L, maxVel, minDist);
-          export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
+          g_last_metadata = r.metadata; export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
 }
 int nbref_init_spiral(int nStars, double totalMass, int nArms, double radius, double thickness, double perturbation,
                       long cap, long* n_out, double* posMass4, double* vel4) {
     try { InitResult r = Initializer::initSpiralGalaxy(nStars, totalMass, nArms, radius, thickness, perturbation);
-          export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
+          g_last_metadata = r.metadata; export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
 }
 int nbref_init_galaxy(int nStars, double bhMass, double mMin, double mMax, double maxPos, double maxVel,
                       int addPlanets, int minPl, int maxPl, double pmMin, double pmMax, double pDist, double pVel,
                       long cap, long* n_out, double* posMass4, double* vel4) {
     try { InitResult r = Initializer::initGalaxy(nStars, bhMass, mMin, mMax, maxPos, maxVel, addPlanets != 0,
                                                  minPl, maxPl, pmMin, pmMax, pDist, pVel);
-          export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
+          g_last_metadata = r.metadata; export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
 }
 int nbref_init_file(const char* path, int count, long cap, long* n_out, double* posMass4, double* vel4) {
     try { InitResult r = Initializer::initFromSistemadat(std::string(path), count);
-          export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
+          g_last_metadata = r.metadata; export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
 }
 
 // The reference's FILE_CSV sink (output/OutputUtils.cpp:8-59) on caller-provided OutputData contents: fixture for the

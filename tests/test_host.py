@@ -144,6 +144,35 @@ def test_host_generators_match_reference_distributions(host, ref):
     assert abs(np.abs(v[:, :3]).mean() - np.abs(rv[:, :3]).mean()) < 0.1
 
 
+def test_generator_metadata_text_matches_the_reference(host, ref):
+    """The "# ..." metadata block each generator contributes to the CSV (core/Initializer.cpp) — compared as text with what
+    the reference's own generators emit for the same parameters (particle values differ: the reference is unseeded)."""
+    ref.l.nbref_last_metadata.restype = C.c_long
+    ref.l.nbref_last_metadata.argtypes = [C.c_char_p, C.c_long]
+
+    def ref_meta():
+        buf = C.create_string_buffer(8192)
+        ref.l.nbref_last_metadata(buf, 8192)
+        return buf.value.decode()
+
+    ref.init_random(600)
+    assert init_from(host, cfg_text(seed=1))[2] == ref_meta()
+    ref.init_spiral(5000)
+    import re
+    mask = lambda t: re.sub(r"(normal\): )\([^)]*\)", r"\1(...)", t)       # the random disc orientation is printed: mask its value
+    ours, theirs = init_from(host, cfg_text(selected="SPIRAL_GALAXY", seed=1))[2], ref_meta()
+    assert "(...)" in mask(ours) and mask(ours) == mask(theirs)
+    ref.init_file(BASE["init"]["FROM_FILE"]["filePath"], 25)
+    assert init_from(host, cfg_text(selected="FROM_FILE"))[2] == ref_meta()
+    g = BASE["init"]["GALAXY"]
+    pm = np.zeros((400, 4)); v = np.zeros((400, 4)); k = C.c_long(0)
+    ref.l.nbref_init_galaxy.argtypes = [C.c_int] + [C.c_double] * 5 + [C.c_int] * 3 + [C.c_double] * 4 + [C.c_long, C.POINTER(C.c_long), nbtest._dp, nbtest._dp]
+    assert ref.l.nbref_init_galaxy(g["nStars"], g["blackHoleMass"], g["starMassMin"], g["starMassMax"], g["maxPosition"], g["maxVelocity"],
+                                   1, g["minPlanets"], g["maxPlanets"], g["planetMassMin"], g["planetMassMax"], g["planetDistanceMax"],
+                                   g["planetVelocityMax"], 400, C.byref(k), nbtest._p(pm), nbtest._p(v)) == 0
+    assert init_from(host, cfg_text(selected="GALAXY", seed=1))[2] == ref_meta()
+
+
 def test_csv_sink_is_byte_identical_to_the_reference_writer(host, ref, tmp_path):
     """FILE_CSV text (metadata, header, fixed 8-digit fields, 15-digit energy): the host's writer against the reference's own
     flushCSVOutput (output/OutputUtils.cpp:8-59, compiled unmodified into oracle/_ref) on the same OutputData contents."""
