@@ -112,6 +112,13 @@ int nbref_init_galaxy(int nStars, double bhMass, double mMin, double mMax, doubl
                                                  minPl, maxPl, pmMin, pmMax, pDist, pVel);
           g_last_metadata = r.metadata; export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
 }
+int nbref_init_stellar(double starMass, int nPlanets, double pmMin, double pmMax, double pdMin, double pdMax, int addMoons,
+                       int minMoons, int maxMoons, double mmMin, double mmMax, double mdMin, double mdMax,
+                       long cap, long* n_out, double* posMass4, double* vel4) {
+    try { InitResult r = Initializer::initStellarSystem(starMass, nPlanets, pmMin, pmMax, pdMin, pdMax, addMoons != 0, minMoons,
+                                                        maxMoons, mmMin, mmMax, mdMin, mdMax);
+          g_last_metadata = r.metadata; export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }
+}
 int nbref_init_file(const char* path, int count, long cap, long* n_out, double* posMass4, double* vel4) {
     try { InitResult r = Initializer::initFromSistemadat(std::string(path), count);
           g_last_metadata = r.metadata; export_particles(r.particles, cap, n_out, posMass4, vel4); return 0; } catch (...) { return 1; }

@@ -171,6 +171,26 @@ def test_generator_metadata_text_matches_the_reference(host, ref):
                                    1, g["minPlanets"], g["maxPlanets"], g["planetMassMin"], g["planetMassMax"], g["planetDistanceMax"],
                                    g["planetVelocityMax"], 400, C.byref(k), nbtest._p(pm), nbtest._p(v)) == 0
     assert init_from(host, cfg_text(selected="GALAXY", seed=1))[2] == ref_meta()
+    # STELLAR_SYSTEM, with the reference's config quirk: moonDistanceMax / moonVelocityMax land in the (moonDistanceMin,
+    # moonDistanceMax) slots (core/ConfigParser.hpp:146-152)
+    q = BASE["init"]["STELLAR_SYSTEM"]
+    ref.l.nbref_init_stellar.argtypes = [C.c_double, C.c_int] + [C.c_double] * 4 + [C.c_int] * 3 + [C.c_double] * 4 + \
+                                        [C.c_long, C.POINTER(C.c_long), nbtest._dp, nbtest._dp]
+    assert ref.l.nbref_init_stellar(q["starMass"], q["nPlanets"], q["planetMassMin"], q["planetMassMax"], q["minPlanetDistance"],
+                                    q["maxPlanetDistance"], 1, q["minMoons"], q["maxMoons"], q["moonMassMin"], q["moonMassMax"],
+                                    q["moonDistanceMax"], q["moonVelocityMax"], 400, C.byref(k), nbtest._p(pm), nbtest._p(v)) == 0
+    mask_n = lambda t: re.sub(r"(Total particle count: )\d+", r"\1N", t)      # 1..3 moons per planet: the count is random
+    hp, hv, hmeta = init_from(host, cfg_text(selected="STELLAR_SYSTEM", seed=1))
+    assert mask_n(hmeta) == mask_n(ref_meta())
+    # same construction on both sides: the star at rest at the origin, planets on circular orbits in the z = 0 plane
+    for P, V, cnt in ((hp, hv, hp.shape[0]), (pm, v, k.value)):
+        assert 1 + 50 * 2 <= cnt <= 1 + 50 * 4 and P[0, 3] == 1.0 and not P[0, :3].any() and not V[0, :3].any()
+        assert not P[:cnt, 2].any() and not V[:cnt, 2].any()
+        r = np.linalg.norm(P[1:cnt, :2], axis=1); sp = np.linalg.norm(V[1:cnt, :2], axis=1)
+        circular = np.isclose(sp, np.sqrt(39.47841760435743 * 1.0 / r), rtol=1e-12, atol=0)   # planets: v = sqrt(G M / r) exactly
+        assert circular.sum() == 50
+        r = r[circular]
+        assert r.min() >= q["minPlanetDistance"] and r.max() <= q["maxPlanetDistance"]
 
 
 def test_csv_sink_is_byte_identical_to_the_reference_writer(host, ref, tmp_path):
