@@ -59,6 +59,19 @@ vel[b:b+c, :3] += 0.5 * (a0[b:b+c] + a1) * dt
 p_ref, v_ref = oracle.step(pm, v, nbtest.VV, nbtest.PAIRWISE, dt, 1)
 assert np.abs(pos[:, :3] - p_ref[:, :3]).max() < 1e-12
 assert np.abs(vel[b:b+c, :3] - v_ref[b:b+c, :3]).max() < 1e-12
+# report points: every rank sums the kinetic energy and the pair potential of its own i-slice against ALL j, then one
+# all-reduce of (K, sum m_i phi_i) — the collective nb_energy (csrc/nb_context.cu) replayed with numpy
+G = 39.47841760435743
+d = pm[b:b+c, None, :3] - pm[None, :, :3]
+r = np.sqrt((d * d).sum(-1))
+with np.errstate(divide="ignore"):
+    inv = np.where(r > 0, 1.0 / r, 0.0)
+phi = (inv * pm[None, :, 3]).sum(1)
+part = torch.tensor([0.5 * (pm[b:b+c, 3] * (v[b:b+c, :3] ** 2).sum(1)).sum(), (pm[b:b+c, 3] * phi).sum()], dtype=torch.float64)
+dist.all_reduce(part)
+e_total = float(part[0]) - 0.5 * G * float(part[1])
+e_ref = oracle.energy(pm, v)
+assert abs(e_total - e_ref) <= 1e-12 * abs(e_ref), (e_total, e_ref)
 dist.destroy_process_group()
 print("gloo rank", rank, "ok")
 '''
