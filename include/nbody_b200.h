@@ -71,7 +71,9 @@ int nb_comm_init(nb_ctx* ctx, const void* id128, int rank, int world);
 /* Host -> device of the whole system (cuda/BenchmarkKernels.cu:40-41). Buffers may be pinned or pageable. On the device
  * the particles are kept in Hilbert-curve order so that a tile of 256 consecutive particles is spatially compact;
  * every entry point that returns per-particle data applies the inverse permutation, so callers only ever see their
- * own order. Multi-GPU: every rank uploads the whole system (all ranks must pass identical arrays). */
+ * own order. Multi-GPU: every rank uploads the whole system (all ranks must pass identical arrays).
+ * FP32-mode contexts return NB_ERR_INVALID for a negative or NaN mass (the far field works in a mass-scaled frame);
+ * FP64-mode contexts take any mass, like the reference's arithmetic. */
 int nb_upload(nb_ctx* ctx, const double* posMass4, const double* vel4);
 /* Device -> host of the final state (cuda/BenchmarkKernels.cu:101-102), all n rows, caller order. Multi-GPU: collective
  * (the slices are all-gathered first), every rank receives the complete state. */
@@ -186,7 +188,8 @@ int nb_run_visualization(long n, double* posMass4, double* vel4, int integration
 /* launchForceKernel(method, blocks, blockSize, smem, stream, d_posMass, d_accel, avgMass, n)
  * (cuda/ForceKernels.cu:208-232). d_posMass4 / d_accel4 are caller-owned device double4 arrays; the context provides
  * the packed-tile scratch. avg_mass <= 0: computed on the device. stream: cudaStream_t (NULL = context stream).
- * The call replaces the context's particle state: nb_step afterwards needs a fresh nb_upload. */
+ * The call replaces the context's particle state: nb_step afterwards needs a fresh nb_upload. Masses are not inspected
+ * here (they are on the device): in an FP32-mode context they must be >= 0. */
 int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, double* d_accel4,
                     double avg_mass, long n, void* stream);
 

@@ -501,7 +501,14 @@ int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
     NB_CUDA(cudaMemcpyAsync(c->stage_vel, vel4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
     // computeAverageMass (core/Forces.cpp:85-95): serial sum in index order on the host, exactly as the reference.
     double total = 0.0;
-    for (long i = 0; i < c->n; ++i) total += posMass4[4 * i + 3];
+    long bad = -1;
+    for (long i = 0; i < c->n; ++i) { const double m = posMass4[4 * i + 3]; total += m; if (!(m >= 0.0) && bad < 0) bad = i; }
+    // The FP32 far field works in a mass-scaled frame (k_j = sqrt(G0 / (G m_j))): a negative or NaN mass would turn into NaN
+    // accelerations for everybody. The reference's arithmetic accepts such input; FP64 mode here does too.
+    if (bad >= 0 && c->precision == NB_PREC_FP32) {
+        NB_CUDA(cudaStreamSynchronize(c->stream));
+        return fail(NB_ERR_INVALID, "nb_upload: particle %ld has mass %g; FP32 mode needs masses >= 0 (use NB_PREC_FP64)", bad, posMass4[4 * bad + 3]);
+    }
     c->avg_mass = total / (double)c->n;
     rc = ingest(c, c->stage_pos, c->stage_vel); if (rc) return rc;
     StepArrays A = arrays(c);

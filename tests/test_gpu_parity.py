@@ -321,6 +321,16 @@ def test_unsupported_methods_fail_cleanly(lib):
             ctx.set_methods(5, PAIRWISE, 1)
 
 
+def test_negative_mass_is_refused_in_fp32_mode_and_exact_in_fp64_mode(lib, oracle):
+    pm, v = nbtest.gen_random(700, seed=31)
+    pm[13, 3] = -2e-6                                   # repels: plain arithmetic in the reference
+    with lib.context(700, FP32) as ctx:
+        ctx.set_methods(VV, PAIRWISE, 1)
+        with pytest.raises(nbtest.NbError, match="mass"):
+            ctx.upload(pm, v)
+    assert nbtest.rel_err(gpu_accel(lib, pm, v, PAIRWISE, FP64), oracle.forces(pm, PAIRWISE)).max() <= 1e-12
+
+
 def test_launch_force_on_caller_device_arrays(lib, oracle):
     """nb_launch_force (= launchForceKernel): caller-owned device double4 arrays, caller's stream."""
     import torch
