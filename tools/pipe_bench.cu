@@ -147,6 +147,27 @@ __global__ void __launch_bounds__(256) k_lds(float* out, float a, float b, int s
     float s = 0; for (int i = 0; i < 8; ++i) s += c[i].x + c[i].y;
     if (s == 12345.f) out[0] = s;
 }
+// 8 FFMA2 + ND DFMA per unit, independent chains: do the FP32x2 and the FP64 pipes run side by side in one instruction stream?
+// (the far kernel leaves the FP64 pipe idle; this is the feasibility number for giving it part of the interactions)
+template <int ND>
+__global__ void __launch_bounds__(256) k_ffma2_dfma(float* out, float a, float b, double da, double db) {
+    float2 c[8]; double d[8]; const float2 A = make_float2(a, a), B = make_float2(b, b);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { c[i] = make_float2(threadIdx.x * 1e-3f + i, i); d[i] = threadIdx.x * 1e-3 + i; }
+#pragma unroll 1
+    for (int it = 0; it < ITERS; ++it) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                c[i] = __ffma2_rn(c[i], A, B);
+                if (i < ND) d[i] = fma(d[i], da, db);
+            }
+        }
+    }
+    float s = 0; for (int i = 0; i < 8; ++i) s += c[i].x + c[i].y + (float)d[i];
+    if (s == 12345.f) out[0] = s;
+}
 __global__ void k_clock(unsigned long long* out, float a, float b) {
     unsigned long long t0, t1, c0, c1;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -201,6 +222,11 @@ int main() {
     run("ffma2x6_mufu0",   [&] { k_ffma2_mufu<0><<<grid, 256>>>(out, 1.0001f, 0.5f); },      (double)ITERS * 48);
     run("ffma2x6_mufu1",   [&] { k_ffma2_mufu<1><<<grid, 256>>>(out, 1.0001f, 0.5f); },      (double)ITERS * 48);
     run("ffma2x6_mufu2",   [&] { k_ffma2_mufu<2><<<grid, 256>>>(out, 1.0001f, 0.5f); },      (double)ITERS * 48);
+    run("ffma2x8_dfma0",   [&] { k_ffma2_dfma<0><<<grid, 256>>>(out, 1.0001f, 0.5f, 1.0001, 0.5); }, (double)ITERS * 64);
+    run("ffma2x8_dfma2",   [&] { k_ffma2_dfma<2><<<grid, 256>>>(out, 1.0001f, 0.5f, 1.0001, 0.5); }, (double)ITERS * 64);
+    run("ffma2x8_dfma4",   [&] { k_ffma2_dfma<4><<<grid, 256>>>(out, 1.0001f, 0.5f, 1.0001, 0.5); }, (double)ITERS * 64);
+    run("ffma2x8_dfma6",   [&] { k_ffma2_dfma<6><<<grid, 256>>>(out, 1.0001f, 0.5f, 1.0001, 0.5); }, (double)ITERS * 64);
+    run("ffma2x8_dfma8",   [&] { k_ffma2_dfma<8><<<grid, 256>>>(out, 1.0001f, 0.5f, 1.0001, 0.5); }, (double)ITERS * 64);
     run("lds128_bcast",    [&] { k_lds<0><<<grid, 256>>>(out, 1.0001f, 0.5f, 1); },          (double)ITERS * 8);
     run("lds128_ffma2x4",  [&] { k_lds<4><<<grid, 256>>>(out, 1.0001f, 0.5f, 1); },          (double)ITERS * 32);
     run("lds128_ffma2x8",  [&] { k_lds<8><<<grid, 256>>>(out, 1.0001f, 0.5f, 1); },          (double)ITERS * 64);
@@ -208,6 +234,6 @@ int main() {
     printf("{\"gpu\": \"%s\", \"sms\": %d, \"sm_ghz_under_fp32_load\": %.4f, \"rates_warp_instr_per_clk_per_sm\": {", p.name, sms, sm_ghz);
     for (size_t i = 0; i < res.size(); ++i)
         printf("%s\"%s\": %.3f", i ? ", " : "", res[i].name.c_str(), res[i].warp_instr_per_clk_per_sm);
-    printf("}, \"note\": \"rate counts the named (primary) instruction only: ffma2x8_selK = FFMA2 rate with K FSETP+FSEL pairs per 8 FFMA2; ffma2x6_mufuK = FFMA2 rate with K MUFU per 6 FFMA2; lds128_ffma2xK = FFMA2 rate with one broadcast LDS.128 per K FFMA2\"}\n");
+    printf("}, \"note\": \"rate counts the named (primary) instruction only: ffma2x8_selK = FFMA2 rate with K FSETP+FSEL pairs per 8 FFMA2; ffma2x6_mufuK = FFMA2 rate with K MUFU per 6 FFMA2; lds128_ffma2xK = FFMA2 rate with one broadcast LDS.128 per K FFMA2; ffma2x8_dfmaK = FFMA2 rate with K DFMA per 8 FFMA2\"}\n");
     return 0;
 }
