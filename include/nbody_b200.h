@@ -150,7 +150,11 @@ int nb_timer_stop(nb_ctx* ctx, float* ms);
  *   "resort_interval"  re-establish the curve order from the current positions every so many steps (default 16; 0 never);
  *                      results stay correct without it, but tiles that lose their compactness take the slower near path
  *   "far_kappa_milli"  1000*kappa of the far-tile criterion box gap > kappa*(half-extent_i + half-extent_j)
- *                      (default 250); 0 = every tile through the near-field path */
+ *                      (default 250); 0 = every tile through the near-field path
+ *   "small_n_fp64"     FP32-mode context, force_variant 0, one GPU: systems of at most this many particles are evaluated
+ *                      by the FP64 kernel (one launch, no near/far split: faster below ~10^4 particles, where a step is
+ *                      latency-bound, and exact to 1e-12). Default 0 for nb_create contexts; the whole-run entry points
+ *                      below use 8192. */
 int nb_set_option(nb_ctx* ctx, const char* key, long value);
 
 /* ---- whole-run entry points with HOST buffers: what the reference's host code binds ------------------------------ */

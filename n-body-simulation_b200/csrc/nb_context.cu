@@ -57,6 +57,9 @@ static int load() {
 #define NB_NCCL(x) do { int _r = (x); if (_r != nccl::kSuccess) return nb::fail(NB_ERR_NCCL, "NCCL error %d (%s): %s", _r, nccl::GetErrorString ? nccl::GetErrorString(_r) : "?", #x); } while (0)
 
 static long round_up(long v, long m) { return (v + m - 1) / m * m; }
+// The one-shot drivers (nb_run_benchmark / nb_run_simulation / nb_run_visualization) send systems up to this size to the
+// FP64 kernel even in FP32 mode; contexts made with nb_create do so only when the "small_n_fp64" option is set.
+constexpr long kSmallSystem = 8192;
 
 } // namespace nb
 
@@ -91,6 +94,7 @@ struct nb_ctx {
     nccl::comm_t comm = nullptr;
     long launches = 0;
     int force_variant = 0, j_splits = 0;
+    long small_n_fp64 = 0;         // FP32-mode context, variant auto, single GPU: systems up to this size use the FP64 kernel
 };
 
 namespace {
@@ -190,9 +194,16 @@ int ensure_part(nb_ctx* c, int S_total) {
     return NB_OK;
 }
 
+// Small systems are latency-bound, not throughput-bound: the FP64 kernel is a single launch (no near/far split, no second
+// stream), faster up to ~10^4 particles (profiles/r01_auto_benchmark_B200*.csv) and exact to 1e-12.
+bool use_fp64_kernel(const nb_ctx* c) {
+    return c->precision == NB_PREC_FP64 ||
+           (c->world == 1 && c->force_variant == 0 && c->small_n_fp64 > 0 && c->n <= c->small_n_fp64);
+}
+
 int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const float* pk, double* part) {
     int rc;
-    if (c->precision == NB_PREC_FP32) {
+    if (!use_fp64_kernel(c)) {
         const int variant = c->force_variant == 0 ? 3 : c->force_variant;
         rc = launch_force_fp32(pk, part, L, c->force, variant, c->stream);
     } else {
@@ -207,8 +218,9 @@ int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const 
 // kernel runs on near_stream next to the FP32 far kernel (different pipes) and writes its own partial slots.
 int eval_force(nb_ctx* c, int* S_out) {
     const int variant = c->force_variant == 0 ? 3 : c->force_variant;
-    const bool split_near = (c->precision == NB_PREC_FP32 && variant == 3);
-    const int R = c->precision == NB_PREC_FP32 ? force_i_tiles_per_cta(variant) : 2;
+    const bool fp64k = use_fp64_kernel(c);
+    const bool split_near = (!fp64k && variant == 3);
+    const int R = fp64k ? 2 : force_i_tiles_per_cta(variant);
     const int nit = (int)(c->ni / kTJ), it0 = (int)(c->i0 / kTJ);
     const int iblocks = nit / R;
     ForceLaunch L; L.it0 = it0; L.nit = nit; L.ntiles = c->ntiles; L.npad = c->npad;
@@ -457,6 +469,7 @@ int nb_set_option(nb_ctx* c, const char* key, long value) {
         return NB_OK;
     }
     if (!strcmp(key, "resort_interval")) { if (value < 0) return fail(NB_ERR_INVALID, "resort_interval must be >= 0"); c->resort_interval = (int)value; return NB_OK; }
+    if (!strcmp(key, "small_n_fp64")) { if (value < 0) return fail(NB_ERR_INVALID, "small_n_fp64 must be >= 0"); c->small_n_fp64 = value; return NB_OK; }
     if (!strcmp(key, "far_kappa_milli")) { if (value < 0) return fail(NB_ERR_INVALID, "far_kappa_milli must be >= 0"); c->kappa = (float)value * 1e-3f; return NB_OK; }
     return fail(NB_ERR_INVALID, "nb_set_option: unknown key '%s'", key);
 }
@@ -739,6 +752,7 @@ int nb_run_benchmark(long n, double* posMass4, double* vel4, int integ, int forc
     (void)block_size;
     nb_ctx* c = nullptr;
     int rc = nb_create(&c, n, device, precision); if (rc) return rc;
+    c->small_n_fp64 = kSmallSystem;
     rc = nb_set_methods(c, integ, force, subtract_com);
     if (!rc) rc = nb_upload(c, posMass4, vel4);
     if (!rc) rc = nb_compute_accel(c);                 // cuda/BenchmarkKernels.cu:68
@@ -756,6 +770,7 @@ int nb_run_simulation(long n, double* posMass4, double* vel4, int integ, int for
     if (num_time_steps < 1) return fail(NB_ERR_INVALID, "nb_run_simulation: num_time_steps=%ld", num_time_steps);
     nb_ctx* c = nullptr;
     int rc = nb_create(&c, n, device, precision); if (rc) return rc;
+    c->small_n_fp64 = kSmallSystem;
     rc = nb_set_methods(c, integ, force, subtract_com);
     if (!rc) rc = nb_upload(c, posMass4, vel4);
     if (!rc) rc = nb_compute_accel(c);                                                     // cuda/SimulationKernels.cu:167
@@ -785,6 +800,7 @@ int nb_run_visualization(long n, double* posMass4, double* vel4, int integ, int 
     std::vector<unsigned char> img((size_t)width * height * 4);
     nb_ctx* c = nullptr;
     int rc = nb_create(&c, n, device, precision); if (rc) return rc;
+    c->small_n_fp64 = kSmallSystem;
     rc = nb_set_methods(c, integ, force, subtract_com);
     if (!rc) rc = nb_upload(c, posMass4, vel4);
     if (!rc) rc = nb_compute_accel(c);                                                   // :118-133

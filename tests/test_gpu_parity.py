@@ -331,6 +331,24 @@ def test_negative_mass_is_refused_in_fp32_mode_and_exact_in_fp64_mode(lib, oracl
     assert nbtest.rel_err(gpu_accel(lib, pm, v, PAIRWISE, FP64), oracle.forces(pm, PAIRWISE)).max() <= 1e-12
 
 
+def test_small_systems_can_be_routed_to_the_fp64_kernel(lib, oracle):
+    """"small_n_fp64": an FP32-mode context evaluates systems up to that size with the FP64 kernel (what the whole-run entry
+    points do up to 8192 particles); above the threshold, or with an explicit force_variant, the FP32 kernels run."""
+    pm, v = nbtest.gen_spiral(3000, seed=14)
+    ref = oracle.forces(pm, PAIRWISE)
+    e_fp32 = nbtest.rel_err(gpu_accel(lib, pm, v, PAIRWISE, FP32), ref).max()
+    e_auto = nbtest.rel_err(gpu_accel(lib, pm, v, PAIRWISE, FP32, small_n_fp64=8192), ref).max()
+    e_above = nbtest.rel_err(gpu_accel(lib, pm, v, PAIRWISE, FP32, small_n_fp64=2999), ref).max()
+    e_forced = nbtest.rel_err(gpu_accel(lib, pm, v, PAIRWISE, FP32, small_n_fp64=8192, force_variant=3), ref).max()
+    assert e_auto <= 1e-12 < e_fp32 <= 1e-5
+    assert e_above == e_fp32 and e_forced == e_fp32
+    # the whole-run entry point at this size lands on the CPU integrator's state to FP64 accuracy even in FP32 mode
+    p1, v1 = pm.copy(), v.copy()
+    lib.check(lib.l.nb_run_benchmark(3000, nbtest._p(p1), nbtest._p(v1), VV, PAIRWISE, 0.01, 5, 256, FP32, 1, -1))
+    p_ref, v_ref = oracle.step(pm, v, VV, PAIRWISE, 0.01, 5)
+    assert np.abs(p1[:, :3] - p_ref[:, :3]).max() <= 1e-9 and np.abs(v1[:, :3] - v_ref[:, :3]).max() <= 1e-9
+
+
 def test_launch_force_on_caller_device_arrays(lib, oracle):
     """nb_launch_force (= launchForceKernel): caller-owned device double4 arrays, caller's stream."""
     import torch
