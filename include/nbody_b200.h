@@ -154,7 +154,10 @@ int nb_timer_stop(nb_ctx* ctx, float* ms);
  *   "small_n_fp64"     FP32-mode context, force_variant 0, one GPU: systems of at most this many particles are evaluated
  *                      by the FP64 kernel (one launch, no near/far split: faster below ~10^4 particles, where a step is
  *                      latency-bound, and exact to 1e-12). Default 0 for nb_create contexts; the whole-run entry points
- *                      below use 8192. */
+ *                      below use 8192.
+ *   "step_graph"       1 = systems of at most 16384 particles on the FP64-kernel route replay one captured step (drift,
+ *                      force, finish, COM) as a CUDA graph instead of four launches; bit-identical results. Default 0
+ *                      for nb_create contexts; the whole-run entry points below switch it on. */
 int nb_set_option(nb_ctx* ctx, const char* key, long value);
 
 /* ---- whole-run entry points with HOST buffers: what the reference's host code binds ------------------------------ */

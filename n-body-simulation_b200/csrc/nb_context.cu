@@ -94,6 +94,9 @@ struct nb_ctx {
     nccl::comm_t comm = nullptr;
     long launches = 0;
     int force_variant = 0, j_splits = 0;
+    // Small systems: one captured step (drift, FP64 force, finish, COM) replayed as a CUDA graph — see step_graph_for().
+    bool step_graph_enabled = false; cudaGraphExec_t step_graph = nullptr;
+    struct StepKey { double dt = 0, avg_mass = 0; int integ = -1, force = -1, sub = -1, S = 0; const void* part = nullptr; } step_key;
     long small_n_fp64 = 0;         // FP32-mode context, variant auto, single GPU: systems up to this size use the FP64 kernel
 };
 
@@ -343,6 +346,53 @@ int resort(nb_ctx* c) {
     return NB_OK;
 }
 
+// ---- small systems: the step as a CUDA graph -------------------------------------------------------------------------
+// Below ~10^4 particles a step is four dependent, microsecond-sized kernels and the cost is launch latency. The one-shot
+// drivers therefore capture that sequence once (same pointers and scalars every step) and replay it; the periodic
+// re-sort stays outside the graph. Only the single-GPU FP64-kernel route is captured: one stream, no events, no allocation.
+int enqueue_small_step(nb_ctx* c, double dt, int S) {
+    StepArrays A = arrays(c);
+    int rc = launch_drift(A, c->integ, dt, c->subtract_com != 0, c->avg_mass, c->stream); if (rc) return rc;
+    ForceLaunch L;
+    L.it0 = 0; L.nit = (int)(c->ni / kTJ); L.jt0 = 0; L.jcount = c->ntiles; L.ntiles = c->ntiles; L.npad = c->npad;
+    L.s0 = 0; L.S = S; L.g0 = 1.f; L.stats_warps = 0; L.stats = nullptr; L.kappa = 0.f;
+    rc = launch_force_fp64(c->pos, c->part, L, c->force, c->avg_mass, c->stream); if (rc) return rc;
+    rc = launch_finish(A, c->integ, c->integ == NB_INTEG_VELOCITY_VERLET, dt, S, c->stream); if (rc) return rc;
+    return launch_com_final(A, c->stream);
+}
+
+void drop_step_graph(nb_ctx* c) {
+    if (c->step_graph) { cudaGraphExecDestroy(c->step_graph); c->step_graph = nullptr; cudaGetLastError(); }
+    c->step_key = nb_ctx::StepKey();
+}
+
+bool step_graph_applies(const nb_ctx* c) {
+    return c->step_graph_enabled && c->world == 1 && use_fp64_kernel(c) && c->n <= 2 * kSmallSystem && !c->collect_stats;
+}
+
+// Returns the executable graph of one step for (dt, methods, mean mass, partial-slot buffer), building it when any of those changed.
+int step_graph_for(nb_ctx* c, double dt, cudaGraphExec_t* out) {
+    const int S = splits_for(c, (int)(c->ni / kTJ) / 2, c->ntiles);
+    int rc = ensure_part(c, S); if (rc) return rc;                   // never inside the capture: it may allocate
+    nb_ctx::StepKey k; k.dt = dt; k.avg_mass = c->avg_mass; k.integ = c->integ; k.force = c->force; k.sub = c->subtract_com; k.S = S; k.part = c->part;
+    const nb_ctx::StepKey& o = c->step_key;
+    if (c->step_graph && o.dt == k.dt && o.avg_mass == k.avg_mass && o.integ == k.integ && o.force == k.force && o.sub == k.sub &&
+        o.S == k.S && o.part == k.part) { *out = c->step_graph; return NB_OK; }
+    drop_step_graph(c);
+    cudaGraph_t g = nullptr;
+    NB_CUDA(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    rc = enqueue_small_step(c, dt, S);
+    const cudaError_t e = cudaStreamEndCapture(c->stream, &g);        // always close the capture, also after a failed enqueue
+    if (rc) { if (g) cudaGraphDestroy(g); cudaGetLastError(); return rc; }
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture", __FILE__, __LINE__);
+    const cudaError_t ei = cudaGraphInstantiate(&c->step_graph, g, 0);
+    cudaGraphDestroy(g);
+    if (ei != cudaSuccess) { c->step_graph = nullptr; return cuda_fail(ei, "cudaGraphInstantiate", __FILE__, __LINE__); }
+    c->step_key = k;
+    *out = c->step_graph;
+    return NB_OK;
+}
+
 int compute_accel(nb_ctx* c, bool kick, double dt) {
     int S = 0;
     int rc = eval_force(c, &S); if (rc) return rc;
@@ -427,6 +477,7 @@ int nb_destroy(nb_ctx* c) {
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     if (c->near_stream) cudaStreamSynchronize(c->near_stream);
     if (c->comm && nccl::CommDestroy) nccl::CommDestroy(c->comm);
+    drop_step_graph(c);
     free_arrays(c);
     cudaFree(c->red); cudaFree(c->eout);
     if (c->ev_packed) cudaEventDestroy(c->ev_packed);
@@ -469,6 +520,7 @@ int nb_set_option(nb_ctx* c, const char* key, long value) {
         return NB_OK;
     }
     if (!strcmp(key, "resort_interval")) { if (value < 0) return fail(NB_ERR_INVALID, "resort_interval must be >= 0"); c->resort_interval = (int)value; return NB_OK; }
+    if (!strcmp(key, "step_graph")) { c->step_graph_enabled = value != 0; if (!value) drop_step_graph(c); return NB_OK; }
     if (!strcmp(key, "small_n_fp64")) { if (value < 0) return fail(NB_ERR_INVALID, "small_n_fp64 must be >= 0"); c->small_n_fp64 = value; return NB_OK; }
     if (!strcmp(key, "far_kappa_milli")) { if (value < 0) return fail(NB_ERR_INVALID, "far_kappa_milli must be >= 0"); c->kappa = (float)value * 1e-3f; return NB_OK; }
     return fail(NB_ERR_INVALID, "nb_set_option: unknown key '%s'", key);
@@ -581,6 +633,17 @@ int nb_step(nb_ctx* c, double dt, int nsteps) {
     int rc = use_device(c); if (rc) return rc;
     if (!c->have_accel) { rc = nb_compute_accel(c); if (rc) return rc; }
     const bool vv = (c->integ == NB_INTEG_VELOCITY_VERLET);
+    if (nsteps > 0 && step_graph_applies(c)) {
+        cudaGraphExec_t exec = nullptr;
+        rc = step_graph_for(c, dt, &exec); if (rc) return rc;
+        for (int s = 0; s < nsteps; ++s) {
+            if (c->resort_interval > 0 && c->steps_since_sort >= c->resort_interval) { rc = resort(c); if (rc) return rc; }
+            c->steps_since_sort++;
+            NB_CUDA(cudaGraphLaunch(exec, c->stream));
+            c->launches += 4;
+        }
+        return NB_OK;
+    }
     for (int s = 0; s < nsteps; ++s) {
         if (c->resort_interval > 0 && c->steps_since_sort >= c->resort_interval) { rc = resort(c); if (rc) return rc; }
         c->steps_since_sort++;
@@ -752,7 +815,7 @@ int nb_run_benchmark(long n, double* posMass4, double* vel4, int integ, int forc
     (void)block_size;
     nb_ctx* c = nullptr;
     int rc = nb_create(&c, n, device, precision); if (rc) return rc;
-    c->small_n_fp64 = kSmallSystem;
+    c->small_n_fp64 = kSmallSystem; c->step_graph_enabled = true;
     rc = nb_set_methods(c, integ, force, subtract_com);
     if (!rc) rc = nb_upload(c, posMass4, vel4);
     if (!rc) rc = nb_compute_accel(c);                 // cuda/BenchmarkKernels.cu:68
@@ -770,7 +833,7 @@ int nb_run_simulation(long n, double* posMass4, double* vel4, int integ, int for
     if (num_time_steps < 1) return fail(NB_ERR_INVALID, "nb_run_simulation: num_time_steps=%ld", num_time_steps);
     nb_ctx* c = nullptr;
     int rc = nb_create(&c, n, device, precision); if (rc) return rc;
-    c->small_n_fp64 = kSmallSystem;
+    c->small_n_fp64 = kSmallSystem; c->step_graph_enabled = true;
     rc = nb_set_methods(c, integ, force, subtract_com);
     if (!rc) rc = nb_upload(c, posMass4, vel4);
     if (!rc) rc = nb_compute_accel(c);                                                     // cuda/SimulationKernels.cu:167
@@ -800,7 +863,7 @@ int nb_run_visualization(long n, double* posMass4, double* vel4, int integ, int 
     std::vector<unsigned char> img((size_t)width * height * 4);
     nb_ctx* c = nullptr;
     int rc = nb_create(&c, n, device, precision); if (rc) return rc;
-    c->small_n_fp64 = kSmallSystem;
+    c->small_n_fp64 = kSmallSystem; c->step_graph_enabled = true;
     rc = nb_set_methods(c, integ, force, subtract_com);
     if (!rc) rc = nb_upload(c, posMass4, vel4);
     if (!rc) rc = nb_compute_accel(c);                                                   // :118-133

@@ -349,6 +349,26 @@ def test_small_systems_can_be_routed_to_the_fp64_kernel(lib, oracle):
     assert np.abs(p1[:, :3] - p_ref[:, :3]).max() <= 1e-9 and np.abs(v1[:, :3] - v_ref[:, :3]).max() <= 1e-9
 
 
+@pytest.mark.parametrize("prec,integ", [(FP32, VV), (FP64, VV), (FP32, EULER)], ids=["fp32-vv", "fp64-vv", "fp32-euler"])
+def test_step_graph_replay_is_bit_identical_to_plain_launches(lib, prec, integ):
+    """Small systems: the whole-run entry points replay one captured step as a CUDA graph ("step_graph"). Same kernels, same
+    order: the state after 40 steps (two periodic re-sorts in between, dt changed once) must equal the plain launches bit for bit."""
+    pm, v = nbtest.gen_galaxy(600, 2, seed=17)
+    states = []
+    for graph in (0, 1):
+        with lib.context(pm.shape[0], prec) as ctx:
+            ctx.set_option("small_n_fp64", 8192)
+            ctx.set_option("step_graph", graph)
+            ctx.set_methods(integ, ADAPTIVE, 1)
+            ctx.upload(pm, v)
+            ctx.step(0.01, 25)
+            ctx.step(0.02, 10)                    # another dt: the graph is rebuilt
+            ctx.step(0.01, 5)
+            states.append(ctx.download() + (ctx.energy(),))
+    assert np.array_equal(states[0][0], states[1][0]) and np.array_equal(states[0][1], states[1][1])
+    assert np.array_equal(states[0][2], states[1][2])
+
+
 def test_launch_force_on_caller_device_arrays(lib, oracle):
     """nb_launch_force (= launchForceKernel): caller-owned device double4 arrays, caller's stream."""
     import torch
