@@ -171,17 +171,27 @@ int check_force_method(int force) {
     return fail(NB_ERR_INVALID, "unknown forceMethod %d", force);
 }
 
+// Small systems are latency-bound, not throughput-bound: the FP64 kernel is a single launch (no near/far split, no second
+// stream), faster up to ~10^4 particles (profiles/r01_auto_benchmark_B200*.csv) and exact to 1e-12.
+bool use_fp64_kernel(const nb_ctx* c) {
+    return c->precision == NB_PREC_FP64 ||
+           (c->world == 1 && c->force_variant == 0 && c->small_n_fp64 > 0 && c->n <= c->small_n_fp64);
+}
+
 int splits_for(nb_ctx* c, int iblocks, int jcount) {
     if (c->j_splits > 0) return c->j_splits < jcount ? c->j_splits : jcount;
     // CTAs of one launch differ a lot in cost (refined tiles, FP64 hand-offs, Hilbert-curve jumps), so the j-range is cut
     // much finer than the sm_count x 2 resident-CTA slots need and the block scheduler does the balancing: measured
     // (profiles/r01_kappa_splits_sweep.json) 64 splits beat the wave-filling choice by 6 % at N = 65536, 4.5 % at 262144
-    // and 1.2 % at 1M. Aim for ~128 CTAs per slot, at least 4 j-tiles per CTA, at most 64 splits, and keep the
+    // and 1.2 % at 1M. Aim for ~128 CTAs per slot, at least 4 j-tiles per CTA (FP32 kernels), at most 64 splits, and keep the
     // partial-sum slots (3 x npad doubles each) under 8 GB.
     const long slots = (long)c->sm_count * 2;
     long S = (128 * slots + iblocks - 1) / (iblocks > 0 ? iblocks : 1);
     if (S > 64) S = 64;
-    if (S > jcount / 4) S = jcount / 4;
+    // the far kernel's bulk-copy ring wants a few tiles per CTA; the FP64 kernel does not, and for a small system its
+    // serial walk over the j-tiles at FP64 latency IS the step time, so there every tile may get its own CTA
+    const int min_tiles = use_fp64_kernel(c) ? 1 : 4;
+    if (S > jcount / min_tiles) S = jcount / min_tiles;
     const long per_slot = 3L * c->npad * (long)sizeof(double);
     const long mem_cap = (8L << 30) / per_slot / 3;        // far A + far B + near may each take this many
     if (S > mem_cap) S = mem_cap;
@@ -195,13 +205,6 @@ int ensure_part(nb_ctx* c, int S_total) {
     NB_CUDA(cudaMalloc(&c->part, need));
     c->part_bytes = need;
     return NB_OK;
-}
-
-// Small systems are latency-bound, not throughput-bound: the FP64 kernel is a single launch (no near/far split, no second
-// stream), faster up to ~10^4 particles (profiles/r01_auto_benchmark_B200*.csv) and exact to 1e-12.
-bool use_fp64_kernel(const nb_ctx* c) {
-    return c->precision == NB_PREC_FP64 ||
-           (c->world == 1 && c->force_variant == 0 && c->small_n_fp64 > 0 && c->n <= c->small_n_fp64);
 }
 
 int launch_one_force(nb_ctx* c, const ForceLaunch& L, const double4* pos, const float* pk, double* part) {
