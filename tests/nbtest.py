@@ -189,6 +189,8 @@ class Lib:
         l.nb_run_simulation.argtypes = [C.c_long, _dp, _dp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
                                         _dp, _dp, _dp, C.c_long, C.c_int, C.c_int, C.c_int]
         l.nb_launch_force.argtypes = [vp, C.c_int, vp, vp, C.c_double, C.c_long, vp]
+        l.nb_run_visualization.argtypes = [C.c_long, _dp, _dp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int,
+                                           C.c_float, C.c_char_p, C.c_int, vp, C.POINTER(C.c_long), C.c_int, C.c_int, C.c_int]
 
     def err(self):
         return self.l.nb_last_error().decode()

@@ -102,3 +102,14 @@ def test_argument_validation_needs_no_gpu(lib):
     assert lib.l.nb_set_methods(None, 0, 0, 1) == 1
     assert lib.l.nb_step(None, 0.1, 1) == 1
     assert lib.l.nb_destroy(None) == 0
+
+
+def test_whole_run_entry_points_validate_before_touching_a_device(lib):
+    pm = np.zeros((4, 4)); v = np.zeros((4, 4)); pm[:, 3] = 1.0; pm[:, 0] = np.arange(4)
+    fr = (C.c_long * 2)()
+    for w, h in ((0, 10), (10, -1), (20000, 10)):
+        assert lib.l.nb_run_visualization(4, nbtest._p(pm), nbtest._p(v), 1, 0, 0.01, 3, 1, w, h, 0.0, None, 1, None, fr, 0, 1, -1) == 1
+        assert "image" in lib.err()
+    assert lib.l.nb_run_visualization(4, nbtest._p(pm), nbtest._p(v), 1, 0, 0.01, -3, 1, 64, 64, 0.0, None, 1, None, fr, 0, 1, -1) == 1
+    # NULL output arrays of the FILE_CSV driver
+    assert lib.l.nb_run_simulation(4, nbtest._p(pm), nbtest._p(v), 1, 0, 0.01, 3, 1, None, None, None, 4, 1, 1, -1) == 1
