@@ -190,7 +190,7 @@ int splits_for(nb_ctx* c, int iblocks, int jcount) {
     if (S > 64) S = 64;
     // the far kernel's bulk-copy ring wants a few tiles per CTA; the FP64 kernel does not, and for a small system its
     // serial walk over the j-tiles at FP64 latency IS the step time, so there every tile may get its own CTA
-    const int min_tiles = use_fp64_kernel(c) ? 1 : 4;
+    const int min_tiles = (use_fp64_kernel(c) && c->world == 1) ? 1 : 4;      // multi-GPU keeps the setting its tests ran with
     if (S > jcount / min_tiles) S = jcount / min_tiles;
     const long per_slot = 3L * c->npad * (long)sizeof(double);
     const long mem_cap = (8L << 30) / per_slot / 3;        // far A + far B + near may each take this many
