@@ -60,6 +60,15 @@ int auto_benchmark(int argc, char** argv) {
 
 int main(int argc, char** argv) {
     try {
+        if (argc > 1 && (std::string(argv[1]) == "--help" || std::string(argv[1]) == "-h")) {
+            std::cout << "usage: nbody_host [config.json]\n"
+                         "       nbody_host --auto-benchmark [--sizes a,b,..] [--forces PAIRWISE,ADAPTIVE_MUTUAL,PAIRWISE_AVX2_FP32]\n"
+                         "                  [--integrators VELOCITY_VERLET,EULER] [--runs K] [--years Y] [--dt D] [--seed S]\n"
+                         "                  [--precision FP32|FP64] [--device I] [--no-warm] [--out file.csv]\n"
+                         "config.json: the reference's keys, plus optional \"seed\", \"precision\", \"subtractCom\", \"device\",\n"
+                         "             \"snapshotOut\", \"frames\" (see n-body-simulation_b200/host/nbh_host.hpp)\n";
+            return 0;
+        }
         if (argc > 1 && std::string(argv[1]) == "--auto-benchmark") return auto_benchmark(argc, argv);   // main.cpp:457-460
         const std::string path = argc > 1 ? argv[1] : "config.json";
         const nbh::Config cfg = nbh::parse_config(path);

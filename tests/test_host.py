@@ -265,6 +265,8 @@ def test_auto_benchmark_statistics_and_csv_schema(host):
 
 
 def test_auto_benchmark_cli_rejects_bad_options():
+    r = subprocess.run([HOST_BIN, "--help"], capture_output=True, text=True)
+    assert r.returncode == 0 and "--auto-benchmark" in r.stdout and "config.json" in r.stdout
     r = subprocess.run([HOST_BIN, "--auto-benchmark", "--forces", "LEAPFROG"], capture_output=True, text=True)
     assert r.returncode == 1 and "unknown force method" in r.stderr
     r = subprocess.run([HOST_BIN, "--auto-benchmark", "--bogus"], capture_output=True, text=True)
