@@ -2,6 +2,9 @@
 #include "nbh_host.hpp"
 
 #include <array>
+#include <charconv>
+#include <cstring>
+#include <vector>
 #include <chrono>
 #include <cmath>
 #include <cstdint>
@@ -323,22 +326,50 @@ InitResult init_spiral_galaxy(int nStars, double totalMass, int nArms, double ga
 
 // output/OutputUtils.cpp:8-59 — metadata, blank line, header, then per snapshot and particle one row with 8-digit fixed
 // floats and the 15-digit energy.
+// Same text as the reference's flushCSVOutput (output/OutputUtils.cpp:8-59: std::fixed, 8 digits, energy 15 digits), but
+// formatted with std::to_chars into a 1 MB buffer instead of ten operator<< calls per row: the file of a large run has
+// tens of millions of rows. tests/test_host.py compares the bytes with the reference writer's.
+namespace {
+inline char* put_fixed(char* p, char* end, double v, int digits) {
+    if (!std::isfinite(v)) {                         // iostream spelling of inf / nan, as the reference would print them
+        std::ostringstream o; o << std::fixed << std::setprecision(digits) << v;
+        const std::string t = o.str();
+        std::memcpy(p, t.data(), t.size());
+        return p + t.size();
+    }
+    const auto r = std::to_chars(p, end, v, std::chars_format::fixed, digits);
+    return r.ptr;
+}
+} // namespace
+
 bool write_csv(const std::string& filename, const std::string& metadata, size_t n, size_t T,
                const double* pd, const double* sd, const double* st) {
-    std::ofstream f(filename);
+    std::ofstream f(filename, std::ios::binary);
     if (!f) { std::cerr << "Could not open CSV file " << filename << " for writing.\n"; return false; }
     f << metadata << "\n" << "particle_id,time,x,y,z,vx,vy,vz,mass,energy\n";
+    constexpr size_t kBuf = 1 << 20, kRowMax = 10 * 340;     // a double in fixed notation has at most ~310 + 17 characters
+    std::vector<char> buf(kBuf + kRowMax);
+    char* p = buf.data();
+    char* const flush_at = buf.data() + kBuf;
+    char* const end = buf.data() + buf.size();
     for (size_t t = 0; t < T; ++t) {
-        const double time = sd[2 * t], energy = sd[2 * t + 1];
+        char tail[2][360];                                   // time and energy repeat for every particle of the snapshot
+        const size_t time_len = (size_t)(put_fixed(tail[0], tail[0] + 360, sd[2 * t], 8) - tail[0]);
+        const size_t energy_len = (size_t)(put_fixed(tail[1], tail[1] + 360, sd[2 * t + 1], 15) - tail[1]);
         for (size_t i = 0; i < n; ++i) {
             const double* q = pd + (t * n + i) * 6;
-            f << std::fixed << std::setprecision(8) << st[2 * i] << "," << time << "," << q[0] << "," << q[1] << "," << q[2] << ","
-              << q[3] << "," << q[4] << "," << q[5] << "," << st[2 * i + 1] << "," << std::fixed << std::setprecision(15) << energy << "\n";
+            p = put_fixed(p, end, st[2 * i], 8); *p++ = ',';
+            std::memcpy(p, tail[0], time_len); p += time_len; *p++ = ',';
+            for (int c = 0; c < 6; ++c) { p = put_fixed(p, end, q[c], 8); *p++ = ','; }
+            p = put_fixed(p, end, st[2 * i + 1], 8); *p++ = ',';
+            std::memcpy(p, tail[1], energy_len); p += energy_len; *p++ = '\n';
+            if (p >= flush_at) { f.write(buf.data(), p - buf.data()); p = buf.data(); }
         }
     }
+    f.write(buf.data(), p - buf.data());
     f.close();
     std::cout << "CSV output written to " << filename << "\n";
-    return true;
+    return (bool)f;
 }
 
 namespace {

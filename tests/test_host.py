@@ -200,6 +200,8 @@ def test_csv_sink_is_byte_identical_to_the_reference_writer(host, ref, tmp_path)
     n, T = 37, 5
     pd = rng.normal(0, 1, (T, n, 6)) * 10.0 ** rng.integers(-9, 7, (T, n, 6))        # tiny, huge, negative values
     pd[0, 0] = [0.0, -0.0, 1e-9, -4.9999999949e-9, 123456789.123456789, -1.0]         # rounding edges of %.8f
+    pd[0, 1] = [np.inf, -np.inf, np.nan, 5e-324, 1.7976931348623157e308, -2.5e-8]     # non-finite, denormal, largest, tie
+    pd[1] *= 10.0 ** rng.integers(-300, 290, (n, 6)).astype(float)                     # the whole double range in one snapshot
     sd = np.stack([np.arange(T) * 0.04, rng.normal(-4e-3, 1e-3, T)], axis=1)
     st = np.stack([np.arange(n, dtype=float), 10.0 ** rng.uniform(-10, 6, n)], axis=1)
     meta = "# years: 100.000000\n# Random particles\n# dt (years): 0.040000\n"
