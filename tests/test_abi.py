@@ -113,3 +113,28 @@ def test_whole_run_entry_points_validate_before_touching_a_device(lib):
     assert lib.l.nb_run_visualization(4, nbtest._p(pm), nbtest._p(v), 1, 0, 0.01, -3, 1, 64, 64, 0.0, None, 1, None, fr, 0, 1, -1) == 1
     # NULL output arrays of the FILE_CSV driver
     assert lib.l.nb_run_simulation(4, nbtest._p(pm), nbtest._p(v), 1, 0, 0.01, 3, 1, None, None, None, 4, 1, 1, -1) == 1
+
+
+def test_partition_bounds_properties(lib):
+    """Any (n, world): the slices are disjoint, ordered, tile-aligned, cover [0, n) exactly and all but the tail have the
+    same padded size (what the all-gather needs)."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=300, deadline=None)
+    @given(n=st.integers(1, 1 << 30), world=st.integers(1, 64))
+    def check(n, world):
+        per = None
+        end = 0
+        for r in range(world):
+            b, c = lib.partition_bounds(n, r, world)
+            assert 0 <= c and b + c <= n
+            if c:
+                assert b == end and b % 1024 == 0
+                end = b + c
+                if b + c < n:                                   # a full slice
+                    per = per or c
+                    assert c == per and c % 1024 == 0
+                elif per:
+                    assert c <= per
+        assert end == n
+    check()
