@@ -194,7 +194,8 @@ int nb_run_visualization(long n, double* posMass4, double* vel4, int integration
 /* ---- device-pointer entry points: the inner boundary of the reference drivers ------------------------------------ */
 /* launchForceKernel(method, blocks, blockSize, smem, stream, d_posMass, d_accel, avgMass, n)
  * (cuda/ForceKernels.cu:208-232). d_posMass4 / d_accel4 are caller-owned device double4 arrays; the context provides
- * the packed-tile scratch. avg_mass <= 0: computed on the device. stream: cudaStream_t (NULL = context stream).
+ * the packed-tile scratch. avg_mass <= 0: computed on the device. stream: cudaStream_t; the call is ordered after the work already
+ * enqueued on it and the stream waits for the result; NULL = the legacy default stream, and the call then also blocks the host until the result is there.
  * The call replaces the context's particle state: nb_step afterwards needs a fresh nb_upload. Masses are not inspected
  * here (they are on the device): in an FP32-mode context they must be >= 0. */
 int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, double* d_accel4,
@@ -208,11 +209,13 @@ int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, dou
  * start-up: plug-ins inside an application whose own pool already owns the device memory (cudaMalloc would fail),
  * per-frame / per-step loops that cannot take cudaMalloc's device-wide synchronisation, jobs with a fixed, declared
  * memory footprint. Limits and rules:
- *   - n <= NB_NOALLOC_MAX_N, otherwise NB_ERR_INVALID with an explanatory message; FP32 pair math (<= 1e-5);
- *   - ADAPTIVE_MUTUAL needs avg_mass > 0 (the mean mass, as the reference's launchForceKernel takes it);
+ *   - n <= NB_NOALLOC_MAX_N, otherwise NB_ERR_INVALID with an explanatory message;
+ *   - PAIRWISE, PAIRWISE_AVX2_FP32 and ADAPTIVE_MUTUAL; ADAPTIVE_MUTUAL needs avg_mass > 0 (the mean mass of the system);
+ *   - FP32 pair math on two-float positions in every pair (no FP64 near field as in a context): NOALLOC_ACCURACY_TEXT
  *   - asynchronous on `stream` (cudaStream_t; NULL = default stream); the device current at the call is used;
  *   - the first call on each device resolves the block's device address; issue it during start-up, before any stream
- *     capture begins;
+ *     capture begins; the address is kept for the life of the process, so do not use this entry point after a
+ *     cudaDeviceReset;
  *   - all calls on a device share the block: calls that overlap on the GPU race — keep them on one stream. */
 #define NB_NOALLOC_MAX_N 32768
 int nb_force_noalloc(int force_method, const double* d_posMass4, double* d_accel4, long n, double avg_mass, void* stream);

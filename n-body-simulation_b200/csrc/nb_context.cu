@@ -911,8 +911,9 @@ int nb_launch_force(nb_ctx* c, int force_method, const double* d_posMass4, doubl
     int rc = check_force_method(force_method); if (rc) return rc;
     rc = use_device(c); if (rc) return rc;
     cudaStream_t user = (cudaStream_t)stream;
-    // Order the context stream after the caller's stream and vice versa with the context's own event.
-    if (user) { NB_CUDA(cudaEventRecord(c->ev_user, user)); NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_user, 0)); }
+    // Order the context stream after the caller's stream and vice versa with the context's own event. A NULL stream is the
+    // legacy default stream: the event recorded on it orders this call after whatever the caller enqueued there.
+    NB_CUDA(cudaEventRecord(c->ev_user, user)); NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_user, 0));
     NB_CUDA(cudaMemcpyAsync(c->stage_pos, d_posMass4, (size_t)n * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
     // The context's particle state is replaced by these positions (velocities zero): a later nb_step needs a new nb_upload.
     c->uploaded = false; c->have_accel = false;

@@ -18,6 +18,8 @@
 // FP64 mode (force_fp64_kernel): same tiling with double4 tiles and DFMA arithmetic.
 #include "nb_common.cuh"
 
+#include <mutex>
+
 namespace nb {
 
 namespace {
@@ -910,11 +912,16 @@ template <int MODE>
 int launch_fp32_mode(const float* pk, double* part, const ForceLaunch& L, int variant, cudaStream_t st) {
     if (variant == 3) {
         if (L.nit % kR4 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR4);
+        // once per device and kernel instance; contexts on different host threads may get here at the same time
+        static std::mutex attr_mutex;
         static bool attr_set[64] = {};
         int dev = 0; NB_CUDA(cudaGetDevice(&dev));
-        if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-            NB_CUDA(cudaFuncSetAttribute(force_fp32_r4_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kR4SmemBytes));
-            attr_set[dev] = true;
+        {
+            std::lock_guard<std::mutex> lock(attr_mutex);
+            if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+                NB_CUDA(cudaFuncSetAttribute(force_fp32_r4_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kR4SmemBytes));
+                if (dev >= 0 && dev < 64) attr_set[dev] = true;
+            }
         }
         dim3 grid(L.nit / kR4, L.S), block(kThreads);
         force_fp32_r4_kernel<MODE><<<grid, block, kR4SmemBytes, st>>>(pk, part, L);

@@ -15,7 +15,9 @@
 //
 // What to know before using it:
 //   * The first call on each device looks up the device address of the block (cudaGetSymbolAddress) and remembers it;
-//     make that first call during start-up, before any stream capture begins.
+//     make that first call during start-up, before any stream capture begins. The remembered address belongs to the
+//     device's current CUDA context: a process that calls cudaDeviceReset afterwards must not use this entry point again
+//     (the address is not looked up a second time; after a reset it may point anywhere).
 //   * Every call on a device uses the same block and leaves its data behind. Nothing in the block needs to be zero
 //     when a call starts: each call writes every word it later reads (tiles incl. padding, all S partial slots).
 //     Two calls that overlap on the GPU (different streams, or different host threads) race on the block and
@@ -45,6 +47,7 @@ namespace {
 constexpr int kMaxDevices = 64;
 std::mutex g_setup_mutex;
 unsigned char* g_scratch_addr[kMaxDevices] = {};       // per device: device address of g_noalloc_scratch on that device
+int g_sm_count[kMaxDevices] = {};                      // per device: number of SMs (sizes the j-splits)
 
 // caller-order double4 positions -> packed tiles (rows 0..7 and 9; the meta row 8 is not read by the variant-1 kernel)
 __global__ void __launch_bounds__(kThreads)
@@ -79,22 +82,25 @@ noalloc_reduce_kernel(const double* __restrict__ part, int S, long npad, long n,
 }
 
 // Device address of the scratch block on the CURRENT device (looked up once per device).
-int scratch_for_current_device(unsigned char** out) {
+int scratch_for_current_device(unsigned char** out, int* sm_count) {
     int dev = 0;
     NB_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= kMaxDevices) return fail(NB_ERR_INVALID, "nb_force_noalloc: device index %d not supported", dev);
     std::lock_guard<std::mutex> lock(g_setup_mutex);
     if (!g_scratch_addr[dev]) {
-        int major = 0;
+        int major = 0, sms = 0;
         NB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
         if (major != 10) return fail(NB_ERR_NO_DEVICE, "nb_force_noalloc: device %d is not sm_100 (this library contains sm_100a code only)", dev);
         void* p = nullptr;
         const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
         if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_noalloc_scratch)", __FILE__, __LINE__);
         if (!p) return fail(NB_ERR_CUDA, "nb_force_noalloc: cudaGetSymbolAddress returned a null address");
+        NB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        g_sm_count[dev] = sms > 0 ? sms : 1;
         g_scratch_addr[dev] = static_cast<unsigned char*>(p);
     }
     *out = g_scratch_addr[dev];
+    *sm_count = g_sm_count[dev];
     return NB_OK;
 }
 
@@ -109,30 +115,31 @@ extern "C" int nb_force_noalloc(int force_method, const double* d_posMass4, doub
     if (n > kNoallocMaxN)
         return fail(NB_ERR_INVALID, "nb_force_noalloc: n=%ld exceeds the built-in scratch capacity of %ld particles "
                                     "(NB_NOALLOC_MAX_N); use a context (nb_create / nb_launch_force) for larger systems", n, kNoallocMaxN);
-    if (force_method == NB_FORCE_BARNES_HUT || force_method == NB_FORCE_PAIRWISE_AVX2_FP32)
-        return fail(NB_ERR_UNSUPPORTED, "nb_force_noalloc: forceMethod %d is reference-only", force_method);
-    if (force_method != NB_FORCE_PAIRWISE && force_method != NB_FORCE_ADAPTIVE_MUTUAL)
+    if (force_method == NB_FORCE_BARNES_HUT)
+        return fail(NB_ERR_UNSUPPORTED, "nb_force_noalloc: forceMethod %d (BARNES_HUT) is not part of this library", force_method);
+    if (force_method != NB_FORCE_PAIRWISE && force_method != NB_FORCE_PAIRWISE_AVX2_FP32 && force_method != NB_FORCE_ADAPTIVE_MUTUAL)
         return fail(NB_ERR_INVALID, "nb_force_noalloc: unknown forceMethod %d", force_method);
     const bool adaptive = (force_method == NB_FORCE_ADAPTIVE_MUTUAL);
     if (adaptive && !(avg_mass > 0.0))
-        return fail(NB_ERR_INVALID, "nb_force_noalloc: ADAPTIVE_MUTUAL needs the mean mass (avg_mass > 0), as the reference's launchForceKernel does");
+        return fail(NB_ERR_INVALID, "nb_force_noalloc: ADAPTIVE_MUTUAL needs the mean mass of the system (avg_mass > 0)");
 
     unsigned char* base = nullptr;
-    int rc = scratch_for_current_device(&base); if (rc) return rc;
-    float*  pk   = reinterpret_cast<float*>(base);
-    double* part = reinterpret_cast<double*>(base + kTilesBytes);
+    int sm_count = 0;
+    int rc = scratch_for_current_device(&base, &sm_count); if (rc) return rc;
 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const long npad = (n + kAlign - 1) / kAlign * kAlign;
     const int ntiles = (int)(npad / kTJ);
     const int iblocks = ntiles / 2;                                  // two i-tiles per CTA
-    int S = (148 * 2 * 4 + iblocks - 1) / iblocks;                   // enough CTAs for a few full waves
+    int S = (sm_count * 2 * 4 + iblocks - 1) / iblocks;              // enough CTAs for a few full waves (2 resident per SM)
     if (S > kNoallocSplits) S = kNoallocSplits;
     if (S > ntiles) S = ntiles;
 
     const double inv3mbar = adaptive ? 1.0 / (3.0 * avg_mass) : 0.0;
+    float* pk = reinterpret_cast<float*>(base);
     noalloc_pack_kernel<<<(unsigned)(npad / kThreads), kThreads, 0, st>>>(reinterpret_cast<const double4*>(d_posMass4), n, pk, inv3mbar);
     NB_CUDA(cudaGetLastError());
+    double* part = reinterpret_cast<double*>(base + kTilesBytes);
 
     ForceLaunch L;
     L.it0 = 0; L.nit = ntiles; L.jt0 = 0; L.jcount = ntiles; L.ntiles = ntiles; L.npad = npad; L.s0 = 0; L.S = S; L.kappa = 3.0e38f; L.g0 = 1.f; L.stats = nullptr; L.stats_warps = 0;

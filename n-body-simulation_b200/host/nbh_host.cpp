@@ -146,8 +146,8 @@ InitResult init_from_file(const std::string& path, int count) {
     for (int i = 0; i < count; ++i) {
         double m, x, y, z, vx, vy, vz;
         f >> m >> x >> y >> z >> vx >> vy >> vz;
-        if (!f.good() && !f.eof()) break;
-        if (f.fail()) break;
+        if (!f.good()) break;          // as the reference (core/Initializer.cpp:36): a last body whose final token ends the file
+                                       // without a trailing newline sets eofbit and is dropped there too
         p.set((size_t)i, m / 1.989e30, x / 1.496e8, y / 1.496e8, z / 1.496e8, vx * 0.2108, vy * 0.2108, vz * 0.2108);
     }
     std::ostringstream md;
