@@ -126,6 +126,13 @@ int nb_last_force_ms(nb_ctx* ctx, float* ms);
 /* Mean duration (ms) of the force evaluations since the last reset (at most the 64 most recent) and how many were
  * averaged; waits for the stream. reset != 0 starts a new measurement window. */
 int nb_force_timing(nb_ctx* ctx, int reset, float* mean_ms, int* evals);
+/* As nb_force_timing, for the FP64 near-field kernel alone (its own stream; it shares the SMs with the far kernel, so this is
+ * its span, not its cost). Call before nb_force_timing(reset=1). evals = 0 on routes without a separate near kernel. */
+int nb_near_timing(nb_ctx* ctx, float* mean_ms, int* evals);
+/* order[k] = caller index of the particle currently in slot k of the device's space-filling-curve order (n entries, host
+ * pointer). Multi-GPU: rank r owns slots [r*per, (r+1)*per), per = nb_partition_bounds' slice length. Lets a checker pick
+ * the particles on either side of a slice boundary. */
+int nb_get_order(nb_ctx* ctx, unsigned int* order);
 /* Diagnostics of the production FP32 kernel (after nb_set_option(ctx, "collect_stats", 1), which also resets them):
  * out[0] j-tiles taken through the CTA-frame far path, out[1] j-tiles refined per warp (both counted once per CTA),
  * out[2] 64-particle sub-tiles through the warp-frame far path, out[3] sub-tiles evaluated in FP64 (once per warp),
@@ -211,7 +218,10 @@ int nb_launch_force(nb_ctx* ctx, int force_method, const double* d_posMass4, dou
  * memory footprint. Limits and rules:
  *   - n <= NB_NOALLOC_MAX_N, otherwise NB_ERR_INVALID with an explanatory message;
  *   - PAIRWISE, PAIRWISE_AVX2_FP32 and ADAPTIVE_MUTUAL; ADAPTIVE_MUTUAL needs avg_mass > 0 (the mean mass of the system);
- *   - FP32 pair math on two-float positions in every pair (no FP64 near field as in a context): NOALLOC_ACCURACY_TEXT
+ *   - FP32 pair math on two-float positions for every pair, FP64 sums; there is no FP64 near field as in a context, so the
+ *     error grows with the cancellation among a particle's nearest neighbours: 2.3e-6 (spiral, 20000), 3.7e-6 (galaxy +
+ *     planets: 4501 ADAPTIVE_MUTUAL; 27001: 2.5e-6 PAIRWISE, 3.5e-6 ADAPTIVE_MUTUAL), 2.1e-6 (12000 particles 6e4 AU from
+ *     the origin) — the largest relative error per particle seen in tests/test_zz_no_alloc.py, whose bound is 1e-5;
  *   - asynchronous on `stream` (cudaStream_t; NULL = default stream); the device current at the call is used;
  *   - the first call on each device resolves the block's device address; issue it during start-up, before any stream
  *     capture begins; the address is kept for the life of the process, so do not use this entry point after a

@@ -66,6 +66,7 @@ int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, in
 int launch_potential_fp64(const double4* pos, double* pot, int it0, int nit, int ntiles, cudaStream_t st);
 int force_regs_info(char* buf, int len);
 int force_i_tiles_per_cta(int variant);
+int force_fp64_i_tiles(long npad, int force_method);
 
 // nb_integrate.cu
 struct StepArrays {

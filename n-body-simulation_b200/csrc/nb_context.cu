@@ -75,6 +75,7 @@ struct nb_ctx {
     cudaEvent_t ev_packed = nullptr, ev_gathered = nullptr, ev_user = nullptr, tev0 = nullptr, tev1 = nullptr;
     static constexpr int kRing = 64;
     cudaEvent_t fev0[kRing] = {}, fev1[kRing] = {};   // ring of force-evaluation event pairs
+    cudaEvent_t nev0[kRing] = {}, nev1[kRing] = {};   // the same for the near kernel alone (near_stream)
     long fev_count = 0;
     char* slab = nullptr; size_t slab_bytes = 0;      // one allocation behind all npad-sized arrays (alloc_arrays)
     double4 *pos = nullptr, *vel = nullptr, *tmp4 = nullptr, *stage_pos = nullptr, *stage_vel = nullptr;
@@ -226,7 +227,7 @@ int eval_force(nb_ctx* c, int* S_out) {
     const int variant = c->force_variant == 0 ? 3 : c->force_variant;
     const bool fp64k = use_fp64_kernel(c);
     const bool split_near = (!fp64k && variant == 3);
-    const int R = fp64k ? 2 : force_i_tiles_per_cta(variant);
+    const int R = fp64k ? force_fp64_i_tiles(c->npad, c->force) : force_i_tiles_per_cta(variant);
     const int nit = (int)(c->ni / kTJ), it0 = (int)(c->i0 / kTJ);
     const int iblocks = nit / R;
     ForceLaunch L; L.it0 = it0; L.nit = nit; L.ntiles = c->ntiles; L.npad = c->npad;
@@ -255,26 +256,35 @@ int eval_force(nb_ctx* c, int* S_out) {
         S_far = SA + SB;
         rc = ensure_part(c, S_far + S_near); if (rc) return rc;
     }
-    if (split_near) {
-        // near field on its own stream: needs the packed tiles (this stream so far) and, multi-GPU, the gathered slices
-        NB_CUDA(cudaEventRecord(c->ev_force_begin, c->stream));
+    // Launch order: the far kernel first, so that its CTAs take the two slots of every SM for as long as it has CTAs left; the
+    // near kernel (128-thread CTAs, low-priority stream) fills what the far kernel's last wave leaves idle.
+    auto launch_near = [&]() -> int {
+        // needs the packed tiles (this stream so far) and, multi-GPU, the gathered slices
         NB_CUDA(cudaStreamWaitEvent(c->near_stream, c->ev_force_begin, 0));
         if (c->world > 1) NB_CUDA(cudaStreamWaitEvent(c->near_stream, c->ev_gathered, 0));
         ForceLaunch N = L; N.jt0 = 0; N.jcount = c->ntiles; N.s0 = S_far; N.S = S_near; N.stats = nullptr;
-        rc = launch_force_near64(c->pk, c->part, N, c->force, c->near_stream); if (rc) return rc;
+        NB_CUDA(cudaEventRecord(c->nev0[slot], c->near_stream));
+        int r2 = launch_force_near64(c->pk, c->part, N, c->force, c->near_stream); if (r2) return r2;
         c->launches++;
+        NB_CUDA(cudaEventRecord(c->nev1[slot], c->near_stream));
         NB_CUDA(cudaEventRecord(c->ev_near_done, c->near_stream));
-    }
+        return NB_OK;
+    };
+    if (split_near) NB_CUDA(cudaEventRecord(c->ev_force_begin, c->stream));
     if (c->world == 1) {
         rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
+        if (split_near) { rc = launch_near(); if (rc) return rc; }
     } else {
         const int SA = splits_for(c, iblocks, nit);
         const int SB = S_far - SA;
-        L.jt0 = it0; L.jcount = nit; L.s0 = 0; L.S = SA;
-        rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
+        ForceLaunch A = L;
+        A.jt0 = it0; A.jcount = nit; A.s0 = 0; A.S = SA;
+        rc = launch_one_force(c, A, c->pos, c->pk, c->part); if (rc) return rc;
+        if (split_near) { rc = launch_near(); if (rc) return rc; }
         NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
-        L.jt0 = (it0 + nit) % c->ntiles; L.jcount = c->ntiles - nit; L.s0 = SA; L.S = SB;
-        rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
+        ForceLaunch B = L;
+        B.jt0 = (it0 + nit) % c->ntiles; B.jcount = c->ntiles - nit; B.s0 = SA; B.S = SB;
+        rc = launch_one_force(c, B, c->pos, c->pk, c->part); if (rc) return rc;
     }
     if (split_near) NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_near_done, 0));
     *S_out = S_far + S_near;
@@ -375,7 +385,7 @@ bool step_graph_applies(const nb_ctx* c) {
 
 // Returns the executable graph of one step for (dt, methods, mean mass, partial-slot buffer), building it when any of those changed.
 int step_graph_for(nb_ctx* c, double dt, cudaGraphExec_t* out) {
-    const int S = splits_for(c, (int)(c->ni / kTJ) / 2, c->ntiles);
+    const int S = splits_for(c, (int)(c->ni / kTJ) / force_fp64_i_tiles(c->npad, c->force), c->ntiles);
     int rc = ensure_part(c, S); if (rc) return rc;                   // never inside the capture: it may allocate
     nb_ctx::StepKey k; k.dt = dt; k.avg_mass = c->avg_mass; k.integ = c->integ; k.force = c->force; k.sub = c->subtract_com; k.S = S; k.part = c->part;
     const nb_ctx::StepKey& o = c->step_key;
@@ -454,9 +464,11 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
     c->i0 = 0; c->ni = c->npad;
     auto bail = [&](int rc) { nb_destroy(c); return rc; };
 #define NB_TRY(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) return bail(cuda_fail(_e, #x, __FILE__, __LINE__)); } while (0)
-    NB_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    NB_TRY(cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
-    NB_TRY(cudaStreamCreateWithFlags(&c->near_stream, cudaStreamNonBlocking));
+    int prio_lo = 0, prio_hi = 0;      // numerically greatest = lowest priority
+    NB_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    NB_TRY(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi));
+    NB_TRY(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, prio_hi));
+    NB_TRY(cudaStreamCreateWithPriority(&c->near_stream, cudaStreamNonBlocking, prio_lo));   // fills what the far kernel leaves
     NB_TRY(cudaEventCreateWithFlags(&c->ev_force_begin, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_near_done, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
@@ -464,6 +476,7 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
     NB_TRY(cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming));
     NB_TRY(cudaEventCreate(&c->tev0)); NB_TRY(cudaEventCreate(&c->tev1));
     for (int k = 0; k < nb_ctx::kRing; ++k) { NB_TRY(cudaEventCreate(&c->fev0[k])); NB_TRY(cudaEventCreate(&c->fev1[k])); }
+    for (int k = 0; k < nb_ctx::kRing; ++k) { NB_TRY(cudaEventCreate(&c->nev0[k])); NB_TRY(cudaEventCreate(&c->nev1[k])); }
     NB_TRY(cudaMalloc(&c->red, 16 * sizeof(double)));
     NB_TRY(cudaMalloc(&c->eout, 16 * sizeof(double)));
     NB_TRY(cudaMemsetAsync(c->red, 0, 16 * sizeof(double), c->stream));
@@ -489,6 +502,7 @@ int nb_destroy(nb_ctx* c) {
     if (c->tev0) cudaEventDestroy(c->tev0);
     if (c->tev1) cudaEventDestroy(c->tev1);
     for (int k = 0; k < nb_ctx::kRing; ++k) { if (c->fev0[k]) cudaEventDestroy(c->fev0[k]); if (c->fev1[k]) cudaEventDestroy(c->fev1[k]); }
+    for (int k = 0; k < nb_ctx::kRing; ++k) { if (c->nev0[k]) cudaEventDestroy(c->nev0[k]); if (c->nev1[k]) cudaEventDestroy(c->nev1[k]); }
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
     if (c->near_stream) cudaStreamDestroy(c->near_stream);
@@ -770,6 +784,36 @@ int nb_force_timing(nb_ctx* c, int reset, float* mean_ms, int* evals) {
     *mean_ms = cnt ? (float)(sum / (double)cnt) : 0.f;
     *evals = (int)cnt;
     if (reset) c->fev_count = 0;
+    return NB_OK;
+}
+
+int nb_near_timing(nb_ctx* c, float* mean_ms, int* evals) {
+    if (!c || !mean_ms || !evals) return fail(NB_ERR_INVALID, "nb_near_timing: NULL argument");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->near_stream));
+    *mean_ms = 0.f; *evals = 0;
+    const int variant = c->force_variant == 0 ? 3 : c->force_variant;
+    if (use_fp64_kernel(c) || variant != 3) return NB_OK;          // no separate near kernel on these routes
+    const long cnt = c->fev_count < nb_ctx::kRing ? c->fev_count : nb_ctx::kRing;
+    double sum = 0.0;
+    for (long k = 0; k < cnt; ++k) {
+        const int slot = (int)((c->fev_count - 1 - k) % nb_ctx::kRing);
+        float ms = 0.f;
+        NB_CUDA(cudaEventElapsedTime(&ms, c->nev0[slot], c->nev1[slot]));
+        sum += ms;
+    }
+    *mean_ms = cnt ? (float)(sum / (double)cnt) : 0.f;
+    *evals = (int)cnt;
+    return NB_OK;
+}
+
+int nb_get_order(nb_ctx* c, unsigned int* order) {
+    if (!c || !order) return fail(NB_ERR_INVALID, "nb_get_order: NULL argument");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_get_order before nb_upload");
+    int rc = use_device(c); if (rc) return rc;
+    NB_CUDA(cudaMemcpyAsync(order, c->perm, (size_t)c->n * sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
 

@@ -571,6 +571,9 @@ __device__ __forceinline__ void load_i_frame(IState4<MODE>& S, const float* __re
     for (int r = 0; r < kR4; ++r) { S.nx[r] = make_float2(xs[r], xs[r]); S.ny[r] = make_float2(ys[r], ys[r]); S.nz[r] = make_float2(zs[r], zs[r]); }
 }
 
+// Register budget: 2 CTAs x 256 threads x 126 registers fill the SM's register file. Capping the kernel at 112 registers
+// would leave room for one 128-thread near-kernel CTA beside them (FP64 pipe busy while the FMA pipe is), but the far loop
+// itself then runs 3.5 % slower (measured: 435.5 instead of 420.3 ms per step at N = 1M) — more than the near kernel costs.
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
@@ -708,38 +711,42 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
 // Warps are independent (no CTA barrier): a warp walks the meta rows of its j-range, skips what the far kernel takes and
 // stages the rare near sub-tile into a warp-private 2 KB buffer. ~0.3 % (N = 1M) to ~4 % (N = 65 536) of all pairs;
 // the kernel runs on its own stream next to the far kernel — the FP64 pipe is idle there.
+// Launch shape: 128-thread CTAs at <= 64 registers (eight resident per SM instead of two 256-thread CTAs at 126 registers:
+// the per-warp work is heavy-tailed, and many small CTAs keep the SMs busy while a long warp finishes). Launched after the
+// far kernel on a low-priority stream, it fills the SMs the far kernel's last wave leaves idle. A far-kernel warp (128
+// i-particles, 4 per lane) is covered by TWO warps here (2 per lane); both classify with the box of the full 128 particles,
+// as the far kernel does.
+constexpr int kNearThreads = 128;
+constexpr int kNearWarps = kNearThreads / 32;
+constexpr int kRN = 2;                         // i-particles per lane
+
 template <int MODE>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __maxnreg__(64)
 force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
-    __shared__ __align__(16) double Jw[kThreads / 32][4][kSubTile];      // x', y', z' (warp frame), G m
-    __shared__ float Mq[kThreads / 32][kSubTile];
+    __shared__ __align__(16) double Jw[kNearWarps][4][kSubTile];      // x', y', z' (warp frame), G m
+    __shared__ float Mq[kNearWarps][kSubTile];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5, s = blockIdx.y;
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
-    const int itile_first = L.it0 + blockIdx.x * kR4;
+    const int itile = L.it0 + blockIdx.x;                               // this CTA: one i-tile = two far-kernel warps
+    const int itile_first = L.it0 + (blockIdx.x / kR4) * kR4;           // the far kernel's CTA (four i-tiles) it belongs to
     Box3 Fbox; float Fhalf, FO[3];
     cta_box(Fbox, Fhalf, FO, pk, itile_first, kR4);
-    const size_t i_first = (size_t)itile_first * kTJ + 4 * (size_t)t;
-    const float* ip = pk + (i_first / kTJ) * kTileFloats + (i_first % kTJ);
+    // the far-kernel warp's 128 particles: lane l looks at 4l..4l+3 (box), and owns 4l + 2h, 4l + 2h + 1 (h = w & 1)
+    const int woff = (w >> 1) * 128 + 4 * lane;
+    const float* ip = pk + (size_t)itile * kTileFloats + woff;
     Box3 Wbox; float Ow[3], Hw;
     warp_box(Wbox, Ow, Hw, ip);
     const float min_gap2 = IS_PLUMMER(MODE) ? 1e-2f : 1e-8f;
-    double xi[kR4], yi[kR4], zi[kR4], mqi[kR4], ax[kR4], ay[kR4], az[kR4];
-    {
-        const float4 xh = *reinterpret_cast<const float4*>(ip + 0 * kTJ), xl = *reinterpret_cast<const float4*>(ip + 4 * kTJ);
-        const float4 yh = *reinterpret_cast<const float4*>(ip + 1 * kTJ), yl = *reinterpret_cast<const float4*>(ip + 5 * kTJ);
-        const float4 zh = *reinterpret_cast<const float4*>(ip + 2 * kTJ), zl = *reinterpret_cast<const float4*>(ip + 6 * kTJ);
-        const float4 mq = *reinterpret_cast<const float4*>(ip + 7 * kTJ);
-        const float h[3][4] = {{xh.x, xh.y, xh.z, xh.w}, {yh.x, yh.y, yh.z, yh.w}, {zh.x, zh.y, zh.z, zh.w}};
-        const float l[3][4] = {{xl.x, xl.y, xl.z, xl.w}, {yl.x, yl.y, yl.z, yl.w}, {zl.x, zl.y, zl.z, zl.w}};
-        const float m[4] = {mq.x, mq.y, mq.z, mq.w};
+    const int own = 2 * (w & 1);
+    double xi[kRN], yi[kRN], zi[kRN], mqi[kRN], ax[kRN], ay[kRN], az[kRN];
 #pragma unroll
-        for (int r = 0; r < kR4; ++r) {
-            xi[r] = ((double)h[0][r] - (double)Ow[0]) + (double)l[0][r];
-            yi[r] = ((double)h[1][r] - (double)Ow[1]) + (double)l[1][r];
-            zi[r] = ((double)h[2][r] - (double)Ow[2]) + (double)l[2][r];
-            mqi[r] = (double)m[r];
-            ax[r] = ay[r] = az[r] = 0.0;
-        }
+    for (int r = 0; r < kRN; ++r) {
+        const float* q = ip + own + r;
+        xi[r] = ((double)q[0 * kTJ] - (double)Ow[0]) + (double)q[4 * kTJ];
+        yi[r] = ((double)q[1 * kTJ] - (double)Ow[1]) + (double)q[5 * kTJ];
+        zi[r] = ((double)q[2 * kTJ] - (double)Ow[2]) + (double)q[6 * kTJ];
+        mqi[r] = IS_ADAPTIVE(MODE) ? (double)q[7 * kTJ] : 0.0;
+        ax[r] = ay[r] = az[r] = 0.0;
     }
     // Scan the j-range 32 tiles at a time: lane l tests tile base + l against the CTA box (the far kernel's first-level
     // test); the warp then visits only the tiles that need refinement (~2 % at N = 1M).
@@ -756,12 +763,12 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
             todo &= todo - 1;
             const float* tile = pk + (size_t)wrap_tile(L.jt0 + k, L.ntiles) * kTileFloats;
             const float* meta = tile + kMetaRow * kTJ;
-    #pragma unroll 1
+#pragma unroll 1
             for (int sb = 0; sb < kTJ / kSubTile; ++sb) {
                 const float* sbox = meta + kSubBoxOffset + 6 * sb;
                 if (boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) continue;      // far kernel, warp frame
                 __syncwarp();
-    #pragma unroll
+#pragma unroll
                 for (int q = lane; q < kSubTile; q += 32) {
                     const float* pj = tile + sb * kSubTile + q;
                     Jw[w][0][q] = ((double)pj[0 * kTJ] - (double)Ow[0]) + (double)pj[4 * kTJ];
@@ -771,12 +778,17 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
                     if (IS_ADAPTIVE(MODE)) Mq[w][q] = pj[7 * kTJ];
                 }
                 __syncwarp();
-    #pragma unroll 2
+                // the 64 interactions of this sub-tile are summed on their own and then added to the running sums: the
+                // running sums see one addition per sub-tile instead of 64 (rounding of close, cancelling neighbours)
+                double sx[kRN], sy[kRN], sz[kRN];
+#pragma unroll
+                for (int r = 0; r < kRN; ++r) sx[r] = sy[r] = sz[r] = 0.0;
+#pragma unroll 2
                 for (int j = 0; j < kSubTile; ++j) {
                     const double xj = Jw[w][0][j], yj = Jw[w][1][j], zj = Jw[w][2][j], gm = Jw[w][3][j];
                     const double mqj = IS_ADAPTIVE(MODE) ? (double)Mq[w][j] : 0.0;
-    #pragma unroll
-                    for (int r = 0; r < kR4; ++r) {
+#pragma unroll
+                    for (int r = 0; r < kRN; ++r) {
                         const double dx = xj - xi[r], dy = yj - yi[r], dz = zj - zi[r];
                         const double r2 = dx * dx + dy * dy + dz * dz;
                         double s2 = r2;
@@ -787,49 +799,62 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
                         if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
                         double sc = gm_inv_r3(s2, gm);
                         if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
-                        ax[r] = fma(sc, dx, ax[r]); ay[r] = fma(sc, dy, ay[r]); az[r] = fma(sc, dz, az[r]);
+                        sx[r] = fma(sc, dx, sx[r]); sy[r] = fma(sc, dy, sy[r]); sz[r] = fma(sc, dz, sz[r]);
                     }
                 }
+#pragma unroll
+                for (int r = 0; r < kRN; ++r) { ax[r] += sx[r]; ay[r] += sy[r]; az[r] += sz[r]; }
             }
         }
     }
-    double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad + i_first;
-    *reinterpret_cast<double4*>(o) = make_double4(ax[0], ax[1], ax[2], ax[3]);
-    *reinterpret_cast<double4*>(o + (size_t)L.npad) = make_double4(ay[0], ay[1], ay[2], ay[3]);
-    *reinterpret_cast<double4*>(o + 2 * (size_t)L.npad) = make_double4(az[0], az[1], az[2], az[3]);
+    double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad + (size_t)itile * kTJ + woff + own;
+    *reinterpret_cast<double2*>(o) = make_double2(ax[0], ax[1]);
+    *reinterpret_cast<double2*>(o + (size_t)L.npad) = make_double2(ay[0], ay[1]);
+    *reinterpret_cast<double2*>(o + 2 * (size_t)L.npad) = make_double2(az[0], az[1]);
 }
 
 // ------------------------------------------------------------------------------------------------------------------
-// FP64 mode. Tiles of 256 double4 (x,y,z,m) straight from the master array; R = 2 i-particles per thread.
-constexpr int kR64 = 2;
-
-template <int MODE>
+// FP64 mode. Tiles of 256 particles straight from the master array, staged as (x, y, z, G m) [+ m / (3 mbar) for
+// ADAPTIVE_MUTUAL] so that nothing that depends on j alone is recomputed per pair; R i-particles per thread (4 for
+// throughput, 2 for small systems where a CTA's serial walk over its j-range is the step time).
+// Each tile's 256 interactions are summed on their own and then added to the running sums (one rounding per tile on
+// the running sum instead of 256): with the particles in curve order consecutive j pull in the same direction, the running
+// sum of a j-range is large compared with the final result, and every addition to it rounds at ITS magnitude.
+template <int MODE, int R>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, const ForceLaunch L, double inv3mbar) {
     __shared__ __align__(16) double4 sm[2][kTJ];
+    __shared__ double smq[IS_ADAPTIVE(MODE) ? 2 : 1][IS_ADAPTIVE(MODE) ? kTJ : 1];
     const int t = threadIdx.x, s = blockIdx.y;
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
-    const int itile_first = L.it0 + blockIdx.x * kR64;
-    double xi[kR64], yi[kR64], zi[kR64], mqi[kR64], ax[kR64], ay[kR64], az[kR64];
+    const int itile_first = L.it0 + blockIdx.x * R;
+    double xi[R], yi[R], zi[R], mqi[R], ax[R], ay[R], az[R];
 #pragma unroll
-    for (int r = 0; r < kR64; ++r) {
+    for (int r = 0; r < R; ++r) {
         const double4 p = pos[(size_t)(itile_first + r) * kTJ + t];
         xi[r] = p.x; yi[r] = p.y; zi[r] = p.z; mqi[r] = p.w * inv3mbar; ax[r] = ay[r] = az[r] = 0.0;
     }
     double4 g = make_double4(0, 0, 0, 0);
-    if (k0 < k1) sm[0][t] = pos[(size_t)wrap_tile(L.jt0 + k0, L.ntiles) * kTJ + t];
+    if (k0 < k1) {
+        g = pos[(size_t)wrap_tile(L.jt0 + k0, L.ntiles) * kTJ + t];
+        if (IS_ADAPTIVE(MODE)) smq[0][t] = g.w * inv3mbar;
+        g.w *= kG;
+        sm[0][t] = g;
+    }
     __syncthreads();
     for (int k = k0; k < k1; ++k) {
         const int b = (k - k0) & 1;
         const bool more = (k + 1 < k1);
         if (more) g = pos[(size_t)wrap_tile(L.jt0 + k + 1, L.ntiles) * kTJ + t];
-#pragma unroll 4
-        for (int j = 0; j < kTJ; ++j) {
-            const double4 pj = sm[b][j];
-            const double gm = kG * pj.w;
-            const double mqj = IS_ADAPTIVE(MODE) ? pj.w * inv3mbar : 0.0;
+        double tx[R], ty[R], tz[R];
 #pragma unroll
-            for (int r = 0; r < kR64; ++r) {
+        for (int r = 0; r < R; ++r) tx[r] = ty[r] = tz[r] = 0.0;
+#pragma unroll (R >= 4 ? 2 : 4)
+        for (int j = 0; j < kTJ; ++j) {
+            const double4 pj = sm[b][j];                       // (x, y, z, G m)
+            const double mqj = IS_ADAPTIVE(MODE) ? smq[IS_ADAPTIVE(MODE) ? b : 0][IS_ADAPTIVE(MODE) ? j : 0] : 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
                 const double dx = pj.x - xi[r], dy = pj.y - yi[r], dz = pj.z - zi[r];
                 const double r2 = dx * dx + dy * dy + dz * dz;
                 double s2 = r2;
@@ -839,23 +864,31 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
                     s2 = fmax(fma(r2 * w, 1e-4, r2), r2 + 1e-8);
                 }
                 if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                  // cuda/ForceKernels.cu:186
-                double sc = gm_inv_r3(s2, gm);
+                double sc = gm_inv_r3(s2, pj.w);
                 // r2 >= 0, so the integer order of the bit patterns is the floating-point order: the cut-off test
                 // (core/Forces.cpp:144) runs on the integer pipe instead of the FP64 pipe.
                 if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;
-                ax[r] = fma(sc, dx, ax[r]); ay[r] = fma(sc, dy, ay[r]); az[r] = fma(sc, dz, az[r]);
+                tx[r] = fma(sc, dx, tx[r]); ty[r] = fma(sc, dy, ty[r]); tz[r] = fma(sc, dz, tz[r]);
             }
         }
-        if (more) sm[b ^ 1][t] = g;
+#pragma unroll
+        for (int r = 0; r < R; ++r) { ax[r] += tx[r]; ay[r] += ty[r]; az[r] += tz[r]; }
+        if (more) {
+            if (IS_ADAPTIVE(MODE)) smq[IS_ADAPTIVE(MODE) ? b ^ 1 : 0][IS_ADAPTIVE(MODE) ? t : 0] = g.w * inv3mbar;
+            g.w *= kG;
+            sm[b ^ 1][t] = g;
+        }
         __syncthreads();
     }
     double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad;
 #pragma unroll
-    for (int r = 0; r < kR64; ++r) {
+    for (int r = 0; r < R; ++r) {
         const size_t i = (size_t)(itile_first + r) * kTJ + t;
         o[i] = ax[r]; o[(size_t)L.npad + i] = ay[r]; o[2 * (size_t)L.npad + i] = az[r];
     }
 }
+
+constexpr int kR64 = 2;   // i-particles per thread of the potential kernel
 
 // Per-particle potential sum_j m_j / r_ij over every pair with r > 0 (core/System.cpp:72-82), FP64.
 __global__ void __launch_bounds__(kThreads, 2)
@@ -939,7 +972,7 @@ int launch_fp32_mode(const float* pk, double* part, const ForceLaunch& L, int va
 int launch_force_near64(const float* pk, double* part, const ForceLaunch& L, int force_method, cudaStream_t st) {
     if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
     if (L.nit % kR4 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR4);
-    dim3 grid(L.nit / kR4, L.S), block(kThreads);
+    dim3 grid(L.nit, L.S), block(kNearThreads);
     switch (force_method) {
         case kPairwise: force_near64_kernel<kPairwise><<<grid, block, 0, st>>>(pk, part, L); break;
         case kPlummer:  force_near64_kernel<kPlummer><<<grid, block, 0, st>>>(pk, part, L); break;
@@ -961,19 +994,29 @@ int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, int f
     return fail(NB_ERR_INVALID, "force: unknown method %d", force_method);
 }
 
-int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st) {
-    if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
-    if (L.nit % kR64 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR64);
-    dim3 grid(L.nit / kR64, L.S), block(kThreads);
+// i-particles per thread of the FP64 kernel: 4 once the system fills the GPU (PAIRWISE: +5 %), 2 for small systems (more,
+// shorter CTAs) and for ADAPTIVE_MUTUAL (4 leave too few registers for the q^(2/3) arithmetic: -5.5 %)
+int force_fp64_i_tiles(long npad, int force_method) { return (npad >= 32768 && force_method != kAdaptive) ? 4 : 2; }
+
+template <int R>
+static int launch_force_fp64_r(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st) {
+    if (L.nit % R != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, R);
+    dim3 grid(L.nit / R, L.S), block(kThreads);
     const double inv3mbar = force_method == kAdaptive ? 1.0 / (3.0 * avg_mass) : 0.0;
     switch (force_method) {
-        case kPairwise: force_fp64_kernel<kPairwise><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
-        case kPlummer:  force_fp64_kernel<kPlummer><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
-        case kAdaptive: force_fp64_kernel<kAdaptive><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
+        case kPairwise: force_fp64_kernel<kPairwise, R><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
+        case kPlummer:  force_fp64_kernel<kPlummer, R><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
+        case kAdaptive: force_fp64_kernel<kAdaptive, R><<<grid, block, 0, st>>>(pos, part, L, inv3mbar); break;
         default: return fail(NB_ERR_INVALID, "force: unknown method %d", force_method);
     }
     NB_CUDA(cudaGetLastError());
     return NB_OK;
+}
+
+int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st) {
+    if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
+    return force_fp64_i_tiles(L.npad, force_method) == 4 ? launch_force_fp64_r<4>(pos, part, L, force_method, avg_mass, st)
+                                           : launch_force_fp64_r<2>(pos, part, L, force_method, avg_mass, st);
 }
 
 int launch_potential_fp64(const double4* pos, double* pot, int it0, int nit, int ntiles, cudaStream_t st) {
@@ -989,7 +1032,7 @@ int force_regs_info(char* buf, int len) {
     return snprintf(buf, len, "fp32_r4:%d fp32_r4_plummer:%d fp32_r4_adaptive:%d fp32_tma:%d fp32_ld:%d fp64:%d fp64_adaptive:%d",
                     regs_of(force_fp32_r4_kernel<kPairwise>), regs_of(force_fp32_r4_kernel<kPlummer>), regs_of(force_fp32_r4_kernel<kAdaptive>),
                     regs_of(force_fp32_tma_kernel<kR32, kPairwise>), regs_of(force_fp32_ld_kernel<kR32, kPairwise>),
-                    regs_of(force_fp64_kernel<kPairwise>), regs_of(force_fp64_kernel<kAdaptive>));
+                    regs_of(force_fp64_kernel<kPairwise, 4>), regs_of(force_fp64_kernel<kAdaptive, 4>));
 }
 
 } // namespace nb

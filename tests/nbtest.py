@@ -183,6 +183,8 @@ class Lib:
         l.nb_set_option.argtypes = [vp, C.c_char_p, C.c_long]
         l.nb_force_timing.argtypes = [vp, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
         l.nb_timer_start.argtypes = [vp]
+        l.nb_near_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+        l.nb_get_order.argtypes = [vp, C.POINTER(C.c_uint)]
         l.nb_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
         l.nb_run_benchmark.argtypes = [C.c_long, _dp, _dp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
                                        C.c_int, C.c_int, C.c_int]
@@ -292,6 +294,16 @@ class Context:
         ms, cnt = C.c_float(0), C.c_int(0)
         self.lib.check(self.l.nb_force_timing(self.h, 1 if reset else 0, C.byref(ms), C.byref(cnt)))
         return ms.value, cnt.value
+
+    def near_timing(self):
+        ms, cnt = C.c_float(0), C.c_int(0)
+        self.lib.check(self.l.nb_near_timing(self.h, C.byref(ms), C.byref(cnt)))
+        return ms.value, cnt.value
+
+    def order(self):
+        o = np.zeros(self.n, dtype=np.uint32)
+        self.lib.check(self.l.nb_get_order(self.h, o.ctypes.data_as(C.POINTER(C.c_uint))))
+        return o
 
     def timer_start(self):
         self.lib.check(self.l.nb_timer_start(self.h))

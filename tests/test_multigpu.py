@@ -98,4 +98,5 @@ def test_sliced_context_matches_single_gpu(args):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                         "--master-addr", "127.0.0.1", "--master-port", "29534", os.path.join(HERE, "mgpu_worker.py")] + args,
                        capture_output=True, text=True, timeout=600)
+    print("\n".join(l for l in r.stdout.splitlines() if l.startswith("rank")))      # shown with -s: kept as the NCCL-path log
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

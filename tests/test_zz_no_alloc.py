@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 
 MAX_N = 32768          # NB_NOALLOC_MAX_N in include/nbody_b200.h
 TOL = 1e-5             # the FP32 tolerance used by tests/test_gpu_parity.py
-CLUSTERED_TOL = 5e-5   # what the header promises for strongly clustered input (see test_noalloc_clustered_input)
+CLUSTERED_TOL = 1e-5   # the same bound on strongly clustered input (observed 3.5e-6; the header quotes the observed values)
 
 
 def _bind(lib):
