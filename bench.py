@@ -296,7 +296,8 @@ def roofline_for(spec, n_sm, f_max, peak_src, rates, per_gpu_interactions, fk_ms
 
 
 class Runner:
-    def __init__(self, lib, rank, world, local_rank):
+    def __init__(self, lib, rank, world, local_rank, opts=()):
+        self.opts = [(kv.split("=")[0], int(kv.split("=")[1])) for kv in opts]
         import torch
         import torch.distributed as dist
         self.torch, self.dist = torch, dist
@@ -340,6 +341,8 @@ class Runner:
         ctx = lib.context(spec["n"], prec, device=self.local)
         if variant:
             ctx.set_option("force_variant", variant)
+        for k, val in self.opts:
+            ctx.set_option(k, val)
         if self.world > 1:
             lib.check(lib.l.nb_comm_init(ctx.h, self.comm_id(), self.rank, self.world))
         ctx.set_methods(nbtest.VV, force, 1)
@@ -409,13 +412,18 @@ class Runner:
         ctx.compute_accel()
         ctx.sync()
         say(f"upload + initial force evaluation done at {time.perf_counter() - t_wall:.1f} s")
+        slice_work = None
+        if world > 1 and spec["n"] <= 2 ** 21:
+            # diagnostic, untimed: one more evaluation of the own slice with no exchange in front of it (the tiles are all there
+            # after the upload), so the ranks do not wait for each other: the time each rank's share of the work takes
+            ctx.force_timing(reset=True); ctx.compute_accel(); ctx.sync()
+            slice_work = self.gather(ctx.force_timing(reset=True)[0])
         if W > 0:
             ctx.step(dt_sim, W); ctx.sync()
             say(f"{W} warm-up step(s) done at {time.perf_counter() - t_wall:.1f} s")
-        sampler = ClockSampler(self.local)
+        sampler = ClockSampler(self.local)      # every rank watches its own GPU; rank 0's record is the line's "clocks"
         self.barrier()
-        if rank == 0:
-            sampler.start(); sampler.wait_first()
+        sampler.start(); sampler.wait_first()
         launches0 = ctx.launches()
         # Device timing: CUDA events recorded on the context's own stream (nb_timer_start/stop); the force-kernel time is
         # the mean over the K evaluations of the event pairs the context records around every force pass.
@@ -428,7 +436,9 @@ class Runner:
         fk_ms, fk_evals = ctx.force_timing(reset=True)
         torch.cuda.synchronize()
         launches = ctx.launches() - launches0
-        clocks = sampler.stop() if rank == 0 else None
+        clocks = sampler.stop()
+        per_rank_mhz = self.gather(clocks["sm_mhz"] or 0.0)
+        per_rank_slow = self.gather(1.0 if set(clocks["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} else 0.0)
         say(f"{K} timed step(s) done at {time.perf_counter() - t_wall:.1f} s")
         t_step = self.max_over_ranks(t_local) / K
         per_rank_force = self.gather(fk_ms)
@@ -441,7 +451,8 @@ class Runner:
                "dtype": "f32" if prec == nbtest.FP32 else "f64", "n_gpus": world, "gpu_launches": launches, "clocks": clocks,
                "per_rank": {"force_ms": {"min": min(per_rank_force), "mean": sum(per_rank_force) / world, "max": max(per_rank_force)},
                             "near_kernel_span_ms": {"min": min(per_rank_near), "mean": sum(per_rank_near) / world, "max": max(per_rank_near)},
-                            "step_ms": {"min": min(per_rank_step), "mean": sum(per_rank_step) / world, "max": max(per_rank_step)}}}
+                            "step_ms": {"min": min(per_rank_step), "mean": sum(per_rank_step) / world, "max": max(per_rank_step)},
+                            "force_ms_by_rank": per_rank_force, "slice_work_ms_by_rank": slice_work, "sm_mhz_by_rank": per_rank_mhz, "ranks_with_slowdown": int(sum(per_rank_slow))}}
         res["_fk_ms"] = max(per_rank_force)
         res["_interactions"] = interactions
         if want_parity:
@@ -485,6 +496,7 @@ def main():
     ap.add_argument("--ref-n", type=int, default=32768, help="sample size of the --impl reference arm")
     ap.add_argument("--configs", default="all", help="extra BASELINE.json configurations in the same line: all | none | comma list of "
                                                      + ",".join(c["id"] for c in EXTRA_CONFIGS))
+    ap.add_argument("--opt", action="append", default=[], help="nb_set_option key=value applied to every context (tuning experiments)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-parity", action="store_true")
@@ -507,7 +519,7 @@ def main():
     assert world == args.gpus or world == 1 and args.gpus == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
 
     lib = nbtest.Lib()
-    runner = Runner(lib, rank, world, local_rank)
+    runner = Runner(lib, rank, world, local_rank, args.opt)
     peaks, peak_src = measured_peaks()
     rates = pipe_rates()
     n_sm = torch.cuda.get_device_properties(local_rank).multi_processor_count
@@ -544,16 +556,18 @@ def main():
     elif not args.no_e2e:
         # multi-GPU: upload (H2D) + step + download (D2H) per timed call through the context API
         Ke = max(1, min(K, 3))
-        ctx.upload(pm, v); ctx.step(dt_sim, 1); lib.check(lib.l.nb_download(ctx.h, nbtest._p(out_pm), nbtest._p(out_v)))   # untimed first call
+        out_idx_t = torch.empty(n, dtype=torch.int32).pin_memory(); out_idx = out_idx_t.numpy().view(np.uint32)
+        ctx.upload(pm, v); ctx.step(dt_sim, 1); ctx.download_slice(out_pm, out_v, out_idx)      # untimed first call
         runner.barrier(); t0 = time.perf_counter()
         for _ in range(Ke):
-            ctx.upload(pm, v); ctx.step(dt_sim, 1); lib.check(lib.l.nb_download(ctx.h, nbtest._p(out_pm), nbtest._p(out_v)))
+            ctx.upload(pm, v); ctx.step(dt_sim, 1); rows = ctx.download_slice(out_pm, out_v, out_idx)[0].shape[0]
         torch.cuda.synchronize()
         t_e = runner.max_over_ranks(time.perf_counter() - t0) / Ke
-        e2e = {"value": 2.0 * interactions / t_e / 1e9, "unit": "Gint/s", "h2d_bytes_per_step": 64 * n * world,
-               "d2h_bytes_per_step": 64 * n * world, "ms_per_call": t_e * 1e3,
-               "call": "per call and rank: nb_upload (H2D) + nb_step(1) (initial force + 1 VV step) + nb_download (D2H): "
-                       "2 force evaluations per call"}
+        e2e = {"value": 2.0 * interactions / t_e / 1e9, "unit": "Gint/s", "h2d_bytes_per_step": 64 * n,
+               "d2h_bytes_per_step": 68 * n, "ms_per_call": t_e * 1e3,
+               "call": "per call, all ranks together: nb_upload (each rank copies its share of the rows H2D, all-gather over NVLink) + "
+                       "nb_step(1) (initial force + 1 VV step) + nb_download_slice (each rank copies its own rows and their caller "
+                       "indices D2H): 2 force evaluations per call; bytes are the sum over ranks"}
     ctx.close()
 
     # ---- the other BASELINE.json configurations at this GPU count

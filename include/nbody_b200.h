@@ -71,13 +71,19 @@ int nb_comm_init(nb_ctx* ctx, const void* id128, int rank, int world);
 /* Host -> device of the whole system (cuda/BenchmarkKernels.cu:40-41). Buffers may be pinned or pageable. On the device
  * the particles are kept in Hilbert-curve order so that a tile of 256 consecutive particles is spatially compact;
  * every entry point that returns per-particle data applies the inverse permutation, so callers only ever see their
- * own order. Multi-GPU: every rank uploads the whole system (all ranks must pass identical arrays).
+ * own order. Multi-GPU: collective; all ranks pass identical arrays holding the whole system, each rank copies only its
+ * share of the rows to its device (rows [ceil(n/world)*rank, ...)) and the shares are all-gathered over NVLink.
  * FP32-mode contexts return NB_ERR_INVALID for a negative or NaN mass (the far field works in a mass-scaled frame);
  * FP64-mode contexts take any mass, like the reference's arithmetic. */
 int nb_upload(nb_ctx* ctx, const double* posMass4, const double* vel4);
 /* Device -> host of the final state (cuda/BenchmarkKernels.cu:101-102), all n rows, caller order. Multi-GPU: collective
  * (the slices are all-gathered first), every rank receives the complete state. */
 int nb_download(nb_ctx* ctx, double* posMass4, double* vel4);
+
+/* Multi-GPU egress without the gather: only the particles this rank owns, in the device's curve order. posMass4 / vel4 /
+ * index receive *count rows (capacity rows must be available; the slice length of nb_partition_bounds suffices); index[k] is
+ * the caller's index of row k. Not collective; the ranks' index sets are disjoint and cover 0..n-1. Single GPU: all n rows. */
+int nb_download_slice(nb_ctx* ctx, double* posMass4, double* vel4, unsigned int* index, long capacity, long* count);
 
 /* a = F(x) for the current positions: the initial launchForceKernel of cuda/BenchmarkKernels.cu:68 /
  * cuda/ForceKernels.cu:208-232. Must precede the first nb_step after an upload (nb_step does it if missing). */

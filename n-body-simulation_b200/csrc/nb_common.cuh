@@ -111,7 +111,13 @@ int launch_snapshot_scatter(const double4* pos, const double4* vel, const unsign
 
 
 // nb_render.cu
-struct RenderState { bool have_mass = false; float min_mass = 1.f, max_mass = 1.f; bool have_vel = false; float smoothed = 0.f; };
+struct RenderState {
+    bool have_mass = false; float min_mass = 1.f, max_mass = 1.f; bool have_vel = false; float smoothed = 0.f;
+    // device scratch kept across frames (grown on demand, never shrunk): [0] what depends on n and the image size,
+    // [1] what depends on the number of fragments. Released with the context (its device current).
+    void* buf[2] = {nullptr, nullptr}; size_t cap[2] = {0, 0};
+    ~RenderState() { cudaFree(buf[0]); cudaFree(buf[1]); cudaGetLastError(); }
+};
 int render_splat(const double4* pos, const double4* vel, const unsigned int* perm, long n, int W, int H,
                  float rot_x, float rot_y, float distance, float tx, float ty, float scale, float point_size, int color_mode,
                  const float color4[4], const float clear4[4], RenderState& st, float* range_out4, unsigned char* h_rgba,

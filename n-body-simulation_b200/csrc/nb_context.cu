@@ -70,8 +70,8 @@ struct nb_ctx {
     long n = 0, npad = 0; int ntiles = 0;
     int integ = NB_INTEG_VELOCITY_VERLET, force = NB_FORCE_PAIRWISE, subtract_com = 1;
     int rank = 0, world = 1; long i0 = 0, ni = 0;
-    cudaStream_t stream = nullptr, comm_stream = nullptr, near_stream = nullptr;
-    cudaEvent_t ev_force_begin = nullptr, ev_near_done = nullptr;
+    cudaStream_t stream = nullptr, comm_stream = nullptr, near_stream = nullptr, far2_stream = nullptr;
+    cudaEvent_t ev_force_begin = nullptr, ev_near_done = nullptr, ev_far2_done = nullptr;
     cudaEvent_t ev_packed = nullptr, ev_gathered = nullptr, ev_user = nullptr, tev0 = nullptr, tev1 = nullptr;
     static constexpr int kRing = 64;
     cudaEvent_t fev0[kRing] = {}, fev1[kRing] = {};   // ring of force-evaluation event pairs
@@ -128,7 +128,7 @@ int alloc_arrays(nb_ctx* c) {
     };
     auto layout = [&]() {
         off = 0;
-        carve(c->pos, np); carve(c->vel, np); carve(c->tmp4, np); carve(c->stage_pos, n); carve(c->stage_vel, n);
+        carve(c->pos, np); carve(c->vel, np); carve(c->tmp4, np); carve(c->stage_pos, np); carve(c->stage_vel, np);
         carve(c->acc, np * 3); carve(c->red_part, (np / kThreads) * 4);
         carve(c->perm, np); carve(c->perm2, np);
         carve(c->ss.keys_in, n); carve(c->ss.keys_out, n); carve(c->ss.idx_in, n);
@@ -238,13 +238,20 @@ int eval_force(nb_ctx* c, int* S_out) {
     const int slot = (int)(c->fev_count % nb_ctx::kRing);
     NB_CUDA(cudaEventRecord(c->fev0[slot], c->stream));
     int S_far = 0, rc;
-    // The near kernel's work per warp is very uneven (a warp whose 128 particles straddle a jump of the Hilbert curve has a
-    // huge box and 50x the median number of FP64 sub-tiles), so its j-range is cut finer than the far kernel's.
+    // The near kernel runs one CTA per (owner = 128 i-particles, j-split). Two opposite costs (measured, N = 1M spiral / 262144
+    // galaxy): without splits the kernel lasts as long as its heaviest owner (an owner straddling an empty stretch of the curve
+    // has a huge box and tens of times the median number of near sub-tiles: 14.3 ms at 1M with one split, 6.8 with 37), with
+    // many splits most CTAs find nothing and cost only their set-up (galaxy: 3.2 ms with 64 splits, 1.8 with one). About 128
+    // j-tiles per CTA, at most 64 splits, and enough CTAs to give every SM a few.
     int S_near = 0;
     if (split_near) {
-        S_near = splits_for(c, iblocks, c->ntiles);
-        const int fine = c->ntiles / 64 < 16 ? (c->ntiles / 64 > 0 ? c->ntiles / 64 : 1) : 16;
-        if (S_near < fine) S_near = fine;
+        const long owners = c->ni / 128;
+        long want = c->ntiles / 128;
+        const long fill = (8L * c->sm_count + owners - 1) / (owners > 0 ? owners : 1);
+        if (want < fill) want = fill;
+        if (want > 64) want = 64;
+        if (want > c->ntiles / 2) want = c->ntiles / 2;
+        S_near = want < 1 ? 1 : (int)want;
     }
     if (c->world == 1) {
         L.jt0 = 0; L.jcount = c->ntiles; L.s0 = 0; L.S = splits_for(c, iblocks, L.jcount);
@@ -270,7 +277,7 @@ int eval_force(nb_ctx* c, int* S_out) {
         NB_CUDA(cudaEventRecord(c->ev_near_done, c->near_stream));
         return NB_OK;
     };
-    if (split_near) NB_CUDA(cudaEventRecord(c->ev_force_begin, c->stream));
+    if (split_near || c->world > 1) NB_CUDA(cudaEventRecord(c->ev_force_begin, c->stream));
     if (c->world == 1) {
         rc = launch_one_force(c, L, c->pos, c->pk, c->part); if (rc) return rc;
         if (split_near) { rc = launch_near(); if (rc) return rc; }
@@ -281,10 +288,19 @@ int eval_force(nb_ctx* c, int* S_out) {
         A.jt0 = it0; A.jcount = nit; A.s0 = 0; A.S = SA;
         rc = launch_one_force(c, A, c->pos, c->pk, c->part); if (rc) return rc;
         if (split_near) { rc = launch_near(); if (rc) return rc; }
-        NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+        // The pass over the remote j-tiles runs on a stream of its own (after the gather): its CTAs start while the last wave
+        // of the own-slice pass drains instead of waiting for it (the two passes write different partial slots).
+        NB_CUDA(cudaStreamWaitEvent(c->far2_stream, c->ev_force_begin, 0));
+        NB_CUDA(cudaStreamWaitEvent(c->far2_stream, c->ev_gathered, 0));
         ForceLaunch B = L;
         B.jt0 = (it0 + nit) % c->ntiles; B.jcount = c->ntiles - nit; B.s0 = SA; B.S = SB;
-        rc = launch_one_force(c, B, c->pos, c->pk, c->part); if (rc) return rc;
+        cudaStream_t main_stream = c->stream;
+        c->stream = c->far2_stream;                      // launch_one_force launches on c->stream
+        rc = launch_one_force(c, B, c->pos, c->pk, c->part);
+        c->stream = main_stream;
+        if (rc) return rc;
+        NB_CUDA(cudaEventRecord(c->ev_far2_done, c->far2_stream));
+        NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_far2_done, 0));
     }
     if (split_near) NB_CUDA(cudaStreamWaitEvent(c->stream, c->ev_near_done, 0));
     *S_out = S_far + S_near;
@@ -415,6 +431,97 @@ int compute_accel(nb_ctx* c, bool kick, double dt) {
     return reduce_com(c);
 }
 
+// ---- FILE_CSV runs: snapshots that do not stop the step loop ---------------------------------------------------------
+// The reference takes its snapshots on a second stream and never synchronises the host inside the loop
+// (cuda/SimulationKernels.cu:55-65,204-217). Here: at a report point the step stream copies the state (caller-order
+// [n][6] rows through the permutation, plus the curve-order positions / velocities the energy needs) into one of kDepth
+// slots and records an event; everything else — the O(N^2) pair potential, the reductions, the device-to-host copies into
+// pinned memory — runs on a low-priority data stream while the next steps are already executing. The host only waits
+// when it reuses a slot (the snapshot taken kDepth report points earlier) and once at the end.
+struct SnapRing {
+    static constexpr int kDepth = 3;
+    nb_ctx* c = nullptr;
+    cudaStream_t stream = nullptr;
+    char* dev = nullptr; char* host = nullptr;
+    double4 *dpos[kDepth] = {}, *dvel[kDepth] = {};
+    double *d6[kDepth] = {}, *dpot[kDepth] = {}, *dred[kDepth] = {}, *dout[kDepth] = {};
+    double *h6[kDepth] = {}, *he[kDepth] = {};
+    cudaEvent_t ready[kDepth] = {}, done[kDepth] = {};
+    double* dst6[kDepth] = {}; double* dstsys[kDepth] = {}; double when[kDepth] = {}; bool busy[kDepth] = {};
+    long taken = 0;
+
+    int init(nb_ctx* ctx) {
+        c = ctx;
+        const size_t np = (size_t)c->npad, n = (size_t)c->n;
+        auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+        const size_t b_state = up(np * sizeof(double4)), b6 = up(n * 6 * sizeof(double)), b_pot = up(np * sizeof(double)),
+                     b_red = up((np / kThreads) * 4 * sizeof(double)), b_out = 256;
+        const size_t per_dev = 2 * b_state + b6 + b_pot + b_red + b_out, per_host = b6 + 256;
+        int lo = 0, hi = 0;
+        NB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        NB_CUDA(cudaStreamCreateWithPriority(&stream, cudaStreamNonBlocking, lo));
+        NB_CUDA(cudaMalloc(&dev, per_dev * kDepth));
+        NB_CUDA(cudaMallocHost(&host, per_host * kDepth));
+        for (int k = 0; k < kDepth; ++k) {
+            char* d = dev + per_dev * k;
+            dpos[k] = reinterpret_cast<double4*>(d); d += b_state;
+            dvel[k] = reinterpret_cast<double4*>(d); d += b_state;
+            d6[k] = reinterpret_cast<double*>(d); d += b6;
+            dpot[k] = reinterpret_cast<double*>(d); d += b_pot;
+            dred[k] = reinterpret_cast<double*>(d); d += b_red;
+            dout[k] = reinterpret_cast<double*>(d);
+            h6[k] = reinterpret_cast<double*>(host + per_host * k);
+            he[k] = reinterpret_cast<double*>(host + per_host * k + b6);
+            NB_CUDA(cudaEventCreateWithFlags(&ready[k], cudaEventDisableTiming));
+            NB_CUDA(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
+        }
+        return NB_OK;
+    }
+    // hand a finished slot to the caller's arrays (host side)
+    int flush(int k) {
+        if (!busy[k]) return NB_OK;
+        NB_CUDA(cudaEventSynchronize(done[k]));
+        memcpy(dst6[k], h6[k], (size_t)c->n * 6 * sizeof(double));
+        dstsys[k][0] = when[k]; dstsys[k][1] = he[k][0];
+        busy[k] = false;
+        return NB_OK;
+    }
+    // snapshot of the state the step stream has reached; particleData6 / systemData2 are filled by a later flush()
+    int take(double time, double* particleData6, double* systemData2) {
+        const int k = (int)(taken % kDepth);
+        int rc = flush(k); if (rc) return rc;
+        const size_t np = (size_t)c->npad;
+        rc = launch_snapshot_scatter(c->pos, c->vel, c->perm, c->n, d6[k], nullptr, c->stream); if (rc) return rc;
+        NB_CUDA(cudaMemcpyAsync(dpos[k], c->pos, np * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+        NB_CUDA(cudaMemcpyAsync(dvel[k], c->vel, np * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+        NB_CUDA(cudaEventRecord(ready[k], c->stream));
+        NB_CUDA(cudaStreamWaitEvent(stream, ready[k], 0));
+        rc = launch_potential_fp64(dpos[k], dpot[k], 0, c->ntiles, c->ntiles, stream); if (rc) return rc;
+        StepArrays A = arrays(c);
+        A.pos = dpos[k]; A.vel = dvel[k]; A.red_part = dred[k];
+        rc = launch_energy_partial(A, dpot[k], 0, c->n, dout[k] + 4, stream); if (rc) return rc;
+        rc = launch_energy_final(dout[k] + 4, dout[k], stream); if (rc) return rc;
+        c->launches += 5;
+        NB_CUDA(cudaMemcpyAsync(h6[k], d6[k], (size_t)c->n * 6 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+        NB_CUDA(cudaMemcpyAsync(he[k], dout[k], 3 * sizeof(double), cudaMemcpyDeviceToHost, stream));
+        NB_CUDA(cudaEventRecord(done[k], stream));
+        dst6[k] = particleData6; dstsys[k] = systemData2; when[k] = time; busy[k] = true;
+        ++taken;
+        return NB_OK;
+    }
+    int drain() {
+        // oldest first, so that a failure leaves a prefix of complete snapshots
+        for (long q = taken >= kDepth ? taken - kDepth : 0; q < taken; ++q) { int rc = flush((int)(q % kDepth)); if (rc) return rc; }
+        return NB_OK;
+    }
+    ~SnapRing() {
+        if (stream) { cudaStreamSynchronize(stream); cudaStreamDestroy(stream); }
+        for (int k = 0; k < kDepth; ++k) { if (ready[k]) cudaEventDestroy(ready[k]); if (done[k]) cudaEventDestroy(done[k]); }
+        cudaFree(dev); cudaFreeHost(host);
+        cudaGetLastError();
+    }
+};
+
 } // namespace
 
 extern "C" {
@@ -468,9 +575,11 @@ int nb_create(nb_ctx** out, long n, int device, int precision) {
     NB_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
     NB_TRY(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi));
     NB_TRY(cudaStreamCreateWithPriority(&c->comm_stream, cudaStreamNonBlocking, prio_hi));
+    NB_TRY(cudaStreamCreateWithPriority(&c->far2_stream, cudaStreamNonBlocking, prio_hi));
     NB_TRY(cudaStreamCreateWithPriority(&c->near_stream, cudaStreamNonBlocking, prio_lo));   // fills what the far kernel leaves
     NB_TRY(cudaEventCreateWithFlags(&c->ev_force_begin, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_near_done, cudaEventDisableTiming));
+    NB_TRY(cudaEventCreateWithFlags(&c->ev_far2_done, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_packed, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
     NB_TRY(cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming));
@@ -492,6 +601,7 @@ int nb_destroy(nb_ctx* c) {
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
     if (c->near_stream) cudaStreamSynchronize(c->near_stream);
+    if (c->far2_stream) cudaStreamSynchronize(c->far2_stream);
     if (c->comm && nccl::CommDestroy) nccl::CommDestroy(c->comm);
     drop_step_graph(c);
     free_arrays(c);
@@ -506,6 +616,8 @@ int nb_destroy(nb_ctx* c) {
     if (c->stream) cudaStreamDestroy(c->stream);
     if (c->comm_stream) cudaStreamDestroy(c->comm_stream);
     if (c->near_stream) cudaStreamDestroy(c->near_stream);
+    if (c->far2_stream) cudaStreamDestroy(c->far2_stream);
+    if (c->ev_far2_done) cudaEventDestroy(c->ev_far2_done);
     if (c->ev_force_begin) cudaEventDestroy(c->ev_force_begin);
     if (c->ev_near_done) cudaEventDestroy(c->ev_near_done);
     cudaGetLastError();
@@ -579,8 +691,23 @@ int nb_comm_init(nb_ctx* c, const void* id128, int rank, int world) {
 int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
     if (!c || !posMass4 || !vel4) return fail(NB_ERR_INVALID, "nb_upload: NULL argument");
     int rc = use_device(c); if (rc) return rc;
-    NB_CUDA(cudaMemcpyAsync(c->stage_pos, posMass4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
-    NB_CUDA(cudaMemcpyAsync(c->stage_vel, vel4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+    if (c->world == 1) {
+        NB_CUDA(cudaMemcpyAsync(c->stage_pos, posMass4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+        NB_CUDA(cudaMemcpyAsync(c->stage_vel, vel4, (size_t)c->n * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+    } else {
+        // Every rank was handed the whole system, but copies only its share of the rows over PCIe (caller order, chunk q =
+        // ceil(n / world)); the chunks are then all-gathered over NVLink (64 B x n x (world-1)/world per rank at hundreds of GB/s
+        // instead of 64 B x n per rank through the host's memory system, all ranks at once).
+        const long q = (c->n + c->world - 1) / c->world;               // q * world <= npad (slices are >= q, rounded up)
+        const long b = q * c->rank < c->n ? q * c->rank : c->n;
+        const long e = b + q < c->n ? b + q : c->n;
+        if (e > b) {
+            NB_CUDA(cudaMemcpyAsync(c->stage_pos + b, posMass4 + 4 * b, (size_t)(e - b) * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+            NB_CUDA(cudaMemcpyAsync(c->stage_vel + b, vel4 + 4 * b, (size_t)(e - b) * sizeof(double4), cudaMemcpyHostToDevice, c->stream));
+        }
+        NB_NCCL(nccl::AllGather((const double*)(c->stage_pos + q * c->rank), (double*)c->stage_pos, (size_t)q * 4, nccl::kFloat64, c->comm, c->stream));
+        NB_NCCL(nccl::AllGather((const double*)(c->stage_vel + q * c->rank), (double*)c->stage_vel, (size_t)q * 4, nccl::kFloat64, c->comm, c->stream));
+    }
     // computeAverageMass (core/Forces.cpp:85-95): serial sum in index order on the host, exactly as the reference.
     double total = 0.0;
     long bad = -1;
@@ -612,6 +739,23 @@ int nb_download(nb_ctx* c, double* posMass4, double* vel4) {
     c->launches += 2;
     NB_CUDA(cudaMemcpyAsync(posMass4, c->stage_pos, (size_t)c->n * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
     NB_CUDA(cudaMemcpyAsync(vel4, c->stage_vel, (size_t)c->n * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+    NB_CUDA(cudaStreamSynchronize(c->stream));
+    return NB_OK;
+}
+
+int nb_download_slice(nb_ctx* c, double* posMass4, double* vel4, unsigned int* index, long capacity, long* count) {
+    if (!c || !posMass4 || !vel4 || !index || !count) return fail(NB_ERR_INVALID, "nb_download_slice: NULL argument");
+    if (!c->uploaded) return fail(NB_ERR_INVALID, "nb_download_slice before nb_upload");
+    int rc = use_device(c); if (rc) return rc;
+    long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;      // the real particles of the own slice
+    *count = e - b;
+    if (capacity < e - b) return fail(NB_ERR_INVALID, "nb_download_slice: capacity %ld < %ld rows owned by this rank", capacity, e - b);
+    if (e > b) {
+        // the master arrays are in curve order: the own slice is contiguous, its caller indices are perm[b..e)
+        NB_CUDA(cudaMemcpyAsync(posMass4, c->pos + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(vel4, c->vel + b, (size_t)(e - b) * sizeof(double4), cudaMemcpyDeviceToHost, c->stream));
+        NB_CUDA(cudaMemcpyAsync(index, c->perm + b, (size_t)(e - b) * sizeof(unsigned int), cudaMemcpyDeviceToHost, c->stream));
+    }
     NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
@@ -886,13 +1030,18 @@ int nb_run_simulation(long n, double* posMass4, double* vel4, int integ, int for
     if (!rc) rc = nb_compute_accel(c);                                                     // cuda/SimulationKernels.cu:167
     if (!rc) rc = nb_snapshot(c, 0.0, h_particleData, h_systemData, h_staticData);          // :171-187 (snapshot 0)
     int counter = 0; long tidx = 1;
-    for (int step = 1; step <= steps && !rc; ++step) {                                     // :193-228
-        rc = nb_step(c, dt, 1);
-        if (!rc && ++counter >= step_freq) {
-            if (tidx < num_time_steps)
-                rc = nb_snapshot(c, step * dt, h_particleData + (size_t)tidx * n * 6, h_systemData + tidx * 2, nullptr);
-            ++tidx; counter = 0;
+    {
+        SnapRing ring;                                                                     // destroyed before the context
+        if (!rc && steps >= step_freq && num_time_steps > 1) rc = ring.init(c);
+        for (int step = 1; step <= steps && !rc; ++step) {                                 // :193-228
+            rc = nb_step(c, dt, 1);
+            if (!rc && ++counter >= step_freq) {
+                if (tidx < num_time_steps)
+                    rc = ring.take(step * dt, h_particleData + (size_t)tidx * n * 6, h_systemData + tidx * 2);
+                ++tidx; counter = 0;
+            }
         }
+        if (!rc) rc = ring.drain();
     }
     if (!rc) rc = nb_download(c, posMass4, vel4);                                          // :246-249
     nb_destroy(c);

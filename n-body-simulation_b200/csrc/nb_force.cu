@@ -574,6 +574,10 @@ __device__ __forceinline__ void load_i_frame(IState4<MODE>& S, const float* __re
 // Register budget: 2 CTAs x 256 threads x 126 registers fill the SM's register file. Capping the kernel at 112 registers
 // would leave room for one 128-thread near-kernel CTA beside them (FP64 pipe busy while the FMA pipe is), but the far loop
 // itself then runs 3.5 % slower (measured: 435.5 instead of 420.3 ms per step at N = 1M) — more than the near kernel costs.
+// Also tried and not kept: the warps of this kernel evaluating their own FP64 near field once the CTA's far loop is done (so
+// that the FP64 pipe works while the SM's other warps keep the FMA pipe busy): 432.7 instead of 420.5 ms per step at N = 1M,
+// 2.21 instead of 2.09 ms at N = 65536 — a CTA keeps its eight warp slots until its slowest warp has finished, and the near
+// work per warp is heavy-tailed.
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
@@ -711,106 +715,102 @@ force_fp32_r4_kernel(const float* __restrict__ pk, double* __restrict__ part, co
 // Warps are independent (no CTA barrier): a warp walks the meta rows of its j-range, skips what the far kernel takes and
 // stages the rare near sub-tile into a warp-private 2 KB buffer. ~0.3 % (N = 1M) to ~4 % (N = 65 536) of all pairs;
 // the kernel runs on its own stream next to the far kernel — the FP64 pipe is idle there.
-// Launch shape: 128-thread CTAs at <= 64 registers (eight resident per SM instead of two 256-thread CTAs at 126 registers:
-// the per-warp work is heavy-tailed, and many small CTAs keep the SMs busy while a long warp finishes). Launched after the
-// far kernel on a low-priority stream, it fills the SMs the far kernel's last wave leaves idle. A far-kernel warp (128
-// i-particles, 4 per lane) is covered by TWO warps here (2 per lane); both classify with the box of the full 128 particles,
-// as the far kernel does.
-constexpr int kNearThreads = 128;
-constexpr int kNearWarps = kNearThreads / 32;
-constexpr int kRN = 2;                         // i-particles per lane
+// Launch shape: ONE far-kernel warp (128 i-particles) per CTA of 256 threads; thread = (i-particle, half of the sub-tile's 64
+// j-particles). What limits this kernel is not the FP64 pipe but the longest chain: the near work of a warp is heavy-tailed
+// (a warp whose 128 particles straddle an empty stretch of the curve has a huge box and tens of times the median number of
+// near sub-tiles), and with one lane per 2-4 i-particles and all 64 j that chain ran for the whole kernel. Eight warps per owner
+// and 32 interactions per thread and sub-tile cut it by 4-8x; every decision is CTA-uniform (one owner), so a sub-tile is staged
+// once per CTA. Launched after the far kernel on a low-priority stream it also fills the SMs the far kernel's last wave
+// leaves idle.
+constexpr int kNearThreads = 256;
+constexpr int kNearOwner = 128;                // i-particles per CTA = one far-kernel warp
 
 template <int MODE>
-__global__ void __maxnreg__(64)
+__global__ void __launch_bounds__(kNearThreads, 4)
 force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, const ForceLaunch L) {
-    __shared__ __align__(16) double Jw[kNearWarps][4][kSubTile];      // x', y', z' (warp frame), G m
-    __shared__ float Mq[kNearWarps][kSubTile];
+    __shared__ __align__(16) double Js[4][kSubTile];                   // x', y', z' (owner frame), G m of the staged sub-tile
+    __shared__ float Mqs[kSubTile];
+    __shared__ int list[kNearThreads];                                 // near tiles of the current round of 256, in order
+    __shared__ int wcount[kNearThreads / 32];
+    __shared__ double red[3][kNearOwner];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5, s = blockIdx.y;
+    const int il = t & (kNearOwner - 1), jh = t / kNearOwner;           // my i-particle, my half of every sub-tile
     const int k0 = (int)(((long)L.jcount * s) / L.S), k1 = (int)(((long)L.jcount * (s + 1)) / L.S);
-    const int itile = L.it0 + blockIdx.x;                               // this CTA: one i-tile = two far-kernel warps
-    const int itile_first = L.it0 + (blockIdx.x / kR4) * kR4;           // the far kernel's CTA (four i-tiles) it belongs to
+    const size_t i_base = (size_t)L.it0 * kTJ + (size_t)blockIdx.x * kNearOwner;     // the owner's first particle
+    const int itile = (int)(i_base / kTJ), off = (int)(i_base % kTJ);
+    const int itile_first = L.it0 + (blockIdx.x / (2 * kR4)) * kR4;     // the far kernel's CTA (four i-tiles, eight warps)
     Box3 Fbox; float Fhalf, FO[3];
     cta_box(Fbox, Fhalf, FO, pk, itile_first, kR4);
-    // the far-kernel warp's 128 particles: lane l looks at 4l..4l+3 (box), and owns 4l + 2h, 4l + 2h + 1 (h = w & 1)
-    const int woff = (w >> 1) * 128 + 4 * lane;
-    const float* ip = pk + (size_t)itile * kTileFloats + woff;
-    Box3 Wbox; float Ow[3], Hw;
-    warp_box(Wbox, Ow, Hw, ip);
+    Box3 Wbox; float Ow[3], Hw;                                         // the owner's box, as the far kernel's warp computes it
+    warp_box(Wbox, Ow, Hw, pk + (size_t)itile * kTileFloats + off + 4 * lane);
     const float min_gap2 = IS_PLUMMER(MODE) ? 1e-2f : 1e-8f;
-    const int own = 2 * (w & 1);
-    double xi[kRN], yi[kRN], zi[kRN], mqi[kRN], ax[kRN], ay[kRN], az[kRN];
-#pragma unroll
-    for (int r = 0; r < kRN; ++r) {
-        const float* q = ip + own + r;
-        xi[r] = ((double)q[0 * kTJ] - (double)Ow[0]) + (double)q[4 * kTJ];
-        yi[r] = ((double)q[1 * kTJ] - (double)Ow[1]) + (double)q[5 * kTJ];
-        zi[r] = ((double)q[2 * kTJ] - (double)Ow[2]) + (double)q[6 * kTJ];
-        mqi[r] = IS_ADAPTIVE(MODE) ? (double)q[7 * kTJ] : 0.0;
-        ax[r] = ay[r] = az[r] = 0.0;
-    }
-    // Scan the j-range 32 tiles at a time: lane l tests tile base + l against the CTA box (the far kernel's first-level
-    // test); the warp then visits only the tiles that need refinement (~2 % at N = 1M).
-    for (int base = k0; base < k1; base += 32) {
-        const int kk = base + lane;
+    const float* q = pk + (size_t)itile * kTileFloats + off + il;
+    const double xi = ((double)q[0 * kTJ] - (double)Ow[0]) + (double)q[4 * kTJ];
+    const double yi = ((double)q[1 * kTJ] - (double)Ow[1]) + (double)q[5 * kTJ];
+    const double zi = ((double)q[2 * kTJ] - (double)Ow[2]) + (double)q[6 * kTJ];
+    const double mqi = IS_ADAPTIVE(MODE) ? (double)q[7 * kTJ] : 0.0;
+    double ax = 0.0, ay = 0.0, az = 0.0;
+    for (int base = k0; base < k1; base += kNearThreads) {
+        // 256 tiles per round against the far kernel's CTA box (its first-level test); ordered compaction of the survivors
+        const int kk = base + t;
         bool refine = false;
         if (kk < k1) {
             const float* m = pk + (size_t)wrap_tile(L.jt0 + kk, L.ntiles) * kTileFloats + kMetaRow * kTJ;
             refine = !boxes_far(Fbox, Fhalf, m, m + 3, L.kappa, min_gap2);
         }
-        unsigned todo = __ballot_sync(0xffffffffu, refine);
-        while (todo) {
-            const int k = base + (__ffs(todo) - 1);
-            todo &= todo - 1;
-            const float* tile = pk + (size_t)wrap_tile(L.jt0 + k, L.ntiles) * kTileFloats;
+        const unsigned bal = __ballot_sync(0xffffffffu, refine);
+        if (lane == 0) wcount[w] = __popc(bal);
+        __syncthreads();
+        int before = 0, total = 0;
+#pragma unroll
+        for (int v = 0; v < kNearThreads / 32; ++v) { const int c = wcount[v]; if (v < w) before += c; total += c; }
+        if (refine) list[before + __popc(bal & ((1u << lane) - 1u))] = kk;
+        __syncthreads();
+        for (int e = 0; e < total; ++e) {
+            const float* tile = pk + (size_t)wrap_tile(L.jt0 + list[e], L.ntiles) * kTileFloats;
             const float* meta = tile + kMetaRow * kTJ;
 #pragma unroll 1
             for (int sb = 0; sb < kTJ / kSubTile; ++sb) {
                 const float* sbox = meta + kSubBoxOffset + 6 * sb;
-                if (boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) continue;      // far kernel, warp frame
-                __syncwarp();
-#pragma unroll
-                for (int q = lane; q < kSubTile; q += 32) {
-                    const float* pj = tile + sb * kSubTile + q;
-                    Jw[w][0][q] = ((double)pj[0 * kTJ] - (double)Ow[0]) + (double)pj[4 * kTJ];
-                    Jw[w][1][q] = ((double)pj[1 * kTJ] - (double)Ow[1]) + (double)pj[5 * kTJ];
-                    Jw[w][2][q] = ((double)pj[2 * kTJ] - (double)Ow[2]) + (double)pj[6 * kTJ];
-                    Jw[w][3][q] = (double)pj[3 * kTJ] + (double)pj[kGmLoRow * kTJ];
-                    if (IS_ADAPTIVE(MODE)) Mq[w][q] = pj[7 * kTJ];
+                if (boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) continue;      // far kernel, warp frame (CTA-uniform)
+                __syncthreads();                                                             // the previous sub-tile is done with
+                if (t < kSubTile) {
+                    const float* pj = tile + sb * kSubTile + t;
+                    Js[0][t] = ((double)pj[0 * kTJ] - (double)Ow[0]) + (double)pj[4 * kTJ];
+                    Js[1][t] = ((double)pj[1 * kTJ] - (double)Ow[1]) + (double)pj[5 * kTJ];
+                    Js[2][t] = ((double)pj[2 * kTJ] - (double)Ow[2]) + (double)pj[6 * kTJ];
+                    Js[3][t] = (double)pj[3 * kTJ] + (double)pj[kGmLoRow * kTJ];
+                    if (IS_ADAPTIVE(MODE)) Mqs[t] = pj[7 * kTJ];
                 }
-                __syncwarp();
-                // the 64 interactions of this sub-tile are summed on their own and then added to the running sums: the
-                // running sums see one addition per sub-tile instead of 64 (rounding of close, cancelling neighbours)
-                double sx[kRN], sy[kRN], sz[kRN];
-#pragma unroll
-                for (int r = 0; r < kRN; ++r) sx[r] = sy[r] = sz[r] = 0.0;
-#pragma unroll 2
-                for (int j = 0; j < kSubTile; ++j) {
-                    const double xj = Jw[w][0][j], yj = Jw[w][1][j], zj = Jw[w][2][j], gm = Jw[w][3][j];
-                    const double mqj = IS_ADAPTIVE(MODE) ? (double)Mq[w][j] : 0.0;
-#pragma unroll
-                    for (int r = 0; r < kRN; ++r) {
-                        const double dx = xj - xi[r], dy = yj - yi[r], dz = zj - zi[r];
-                        const double r2 = dx * dx + dy * dy + dz * dz;
-                        double s2 = r2;
-                        if (IS_ADAPTIVE(MODE)) {
-                            const double wq = pow23(mqi[r] + mqj);
-                            s2 = fmax(fma(r2 * wq, 1e-4, r2), r2 + 1e-8);
-                        }
-                        if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
-                        double sc = gm_inv_r3(s2, gm);
-                        if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
-                        sx[r] = fma(sc, dx, sx[r]); sy[r] = fma(sc, dy, sy[r]); sz[r] = fma(sc, dz, sz[r]);
+                __syncthreads();
+                // the interactions of one sub-tile are summed on their own and then added to the running sums
+                double sx = 0.0, sy = 0.0, sz = 0.0;
+                const int j0 = jh * (kSubTile / 2);
+#pragma unroll 4
+                for (int j = j0; j < j0 + kSubTile / 2; ++j) {
+                    const double dx = Js[0][j] - xi, dy = Js[1][j] - yi, dz = Js[2][j] - zi, gm = Js[3][j];
+                    const double r2 = dx * dx + dy * dy + dz * dz;
+                    double s2 = r2;
+                    if (IS_ADAPTIVE(MODE)) {
+                        const double wq = pow23(mqi + (double)Mqs[j]);
+                        s2 = fmax(fma(r2 * wq, 1e-4, r2), r2 + 1e-8);
                     }
+                    if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
+                    double sc = gm_inv_r3(s2, gm);
+                    if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
+                    sx = fma(sc, dx, sx); sy = fma(sc, dy, sy); sz = fma(sc, dz, sz);
                 }
-#pragma unroll
-                for (int r = 0; r < kRN; ++r) { ax[r] += sx[r]; ay[r] += sy[r]; az[r] += sz[r]; }
+                ax += sx; ay += sy; az += sz;
             }
         }
+        __syncthreads();                                                                     // list / wcount are rewritten next round
     }
-    double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad + (size_t)itile * kTJ + woff + own;
-    *reinterpret_cast<double2*>(o) = make_double2(ax[0], ax[1]);
-    *reinterpret_cast<double2*>(o + (size_t)L.npad) = make_double2(ay[0], ay[1]);
-    *reinterpret_cast<double2*>(o + 2 * (size_t)L.npad) = make_double2(az[0], az[1]);
+    if (jh == 1) { red[0][il] = ax; red[1][il] = ay; red[2][il] = az; }
+    __syncthreads();
+    if (jh == 0) {
+        double* o = part + (size_t)(L.s0 + s) * 3 * (size_t)L.npad + i_base + il;
+        o[0] = ax + red[0][il]; o[(size_t)L.npad] = ay + red[1][il]; o[2 * (size_t)L.npad] = az + red[2][il];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -820,6 +820,11 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
 // Each tile's 256 interactions are summed on their own and then added to the running sums (one rounding per tile on
 // the running sum instead of 256): with the particles in curve order consecutive j pull in the same direction, the running
 // sum of a j-range is large compared with the final result, and every addition to it rounds at ITS magnitude.
+#ifndef NB_FP64_UNROLL4
+#define NB_FP64_UNROLL4 4
+#endif
+constexpr int kFp64Unroll4 = NB_FP64_UNROLL4;      // j-particles per iteration of the inner loop with 4 i-particles per thread
+
 template <int MODE, int R>
 __global__ void __launch_bounds__(kThreads, 2)
 force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, const ForceLaunch L, double inv3mbar) {
@@ -849,7 +854,7 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
         double tx[R], ty[R], tz[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) tx[r] = ty[r] = tz[r] = 0.0;
-#pragma unroll (R >= 4 ? 2 : 4)
+#pragma unroll (R >= 4 ? kFp64Unroll4 : 4)
         for (int j = 0; j < kTJ; ++j) {
             const double4 pj = sm[b][j];                       // (x, y, z, G m)
             const double mqj = IS_ADAPTIVE(MODE) ? smq[IS_ADAPTIVE(MODE) ? b : 0][IS_ADAPTIVE(MODE) ? j : 0] : 0.0;
@@ -890,12 +895,22 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
 
 constexpr int kR64 = 2;   // i-particles per thread of the potential kernel
 
-// Per-particle potential sum_j m_j / r_ij over every pair with r > 0 (core/System.cpp:72-82), FP64.
+// Pair potential for computeTotalEnergy (core/System.cpp:72-82: every pair with r > 0, unsoftened), FP64, each unordered
+// pair evaluated ONCE like the reference's kernel (cuda/IntegrationKernels.cu:128, `if (i < idx)`), but balanced: the
+// particle in tile I sums m_j / r over its own tile with weight 1/2, over the next h = (T-1)/2 tiles of the circular tile
+// order with weight 1 and — T even — over the antipodal tile I + T/2 with weight 1/2. Every unordered pair of particles then
+// appears with total weight 1 (pairs in one tile and antipodal pairs from both sides with 1/2 each), every i-tile does the same
+// T/2 + 1 tile passes, and a multi-GPU rank can do this for its own i-slice alone. pot[i] = sum_j w m_j / r_ij, so that
+// E_pot = -G sum_i m_i pot[i]. The reciprocal root is the branch-free MUFU seed + second-order correction used by the force
+// kernels (12 DP operations per pair); a tile's 256 terms are summed on their own before they join the running sum.
 __global__ void __launch_bounds__(kThreads, 2)
 potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot, int it0, int ntiles) {
     __shared__ __align__(16) double4 sm[2][kTJ];
     const int t = threadIdx.x;
     const int itile_first = it0 + blockIdx.x * kR64;
+    const int h = (ntiles - 1) / 2;
+    const bool even = (ntiles % 2) == 0;
+    const int span = kR64 + h + (even ? 1 : 0);            // tiles itile_first + 0 .. span-1 cover every i-tile's window
     double xi[kR64], yi[kR64], zi[kR64], acc[kR64];
 #pragma unroll
     for (int r = 0; r < kR64; ++r) {
@@ -903,23 +918,42 @@ potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot,
         xi[r] = p.x; yi[r] = p.y; zi[r] = p.z; acc[r] = 0.0;
     }
     double4 g = make_double4(0, 0, 0, 0);
-    sm[0][t] = pos[t];
+    sm[0][t] = pos[(size_t)(itile_first % ntiles) * kTJ + t];
     __syncthreads();
-    for (int k = 0; k < ntiles; ++k) {
+    for (int k = 0; k < span; ++k) {
         const int b = k & 1;
-        const bool more = (k + 1 < ntiles);
-        if (more) g = pos[(size_t)(k + 1) * kTJ + t];
-#pragma unroll 4
-        for (int j = 0; j < kTJ; ++j) {
-            const double4 pj = sm[b][j];
+        const bool more = (k + 1 < span);
+        if (more) g = pos[(size_t)((itile_first + k + 1) % ntiles) * kTJ + t];
+        double w[kR64];
+        bool any = false;
 #pragma unroll
-            for (int r = 0; r < kR64; ++r) {
-                const double dx = pj.x - xi[r], dy = pj.y - yi[r], dz = pj.z - zi[r];
-                const double r2 = dx * dx + dy * dy + dz * dz;
-                double ri = rsqrt(r2);
-                ri = r2 > 0.0 ? ri : 0.0;
-                acc[r] += pj.w * ri;
+        for (int r = 0; r < kR64; ++r) {
+            const int d = k - r;                             // distance of this tile from i-tile itile_first + r
+            w[r] = d == 0 ? 0.5 : (d >= 1 && d <= h) ? 1.0 : (even && d == h + 1) ? 0.5 : 0.0;
+            any = any || w[r] != 0.0;
+        }
+        if (any) {
+            double ts[kR64];
+#pragma unroll
+            for (int r = 0; r < kR64; ++r) ts[r] = 0.0;
+#pragma unroll 4
+            for (int j = 0; j < kTJ; ++j) {
+                const double4 pj = sm[b][j];
+#pragma unroll
+                for (int r = 0; r < kR64; ++r) {
+                    const double dx = pj.x - xi[r], dy = pj.y - yi[r], dz = pj.z - zi[r];
+                    const double r2 = dx * dx + dy * dy + dz * dz;
+                    const double y0 = rsq64_seed(r2);
+                    const double e = fma(r2, -(y0 * y0), 1.0);
+                    const double c = e * fma(e, 0.375, 0.5);
+                    double mri = pj.w * fma(y0, c, y0);
+                    mri = __double_as_longlong(r2) < 0x0010000000000000LL ? 0.0 : mri;   // r > 0 only (self pair, coincident particles, pads;
+                                                                                             // the MUFU seed flushes subnormal r^2 to zero)
+                    ts[r] += mri;
+                }
             }
+#pragma unroll
+            for (int r = 0; r < kR64; ++r) acc[r] = fma(w[r], ts[r], acc[r]);
         }
         if (more) sm[b ^ 1][t] = g;
         __syncthreads();
@@ -972,7 +1006,7 @@ int launch_fp32_mode(const float* pk, double* part, const ForceLaunch& L, int va
 int launch_force_near64(const float* pk, double* part, const ForceLaunch& L, int force_method, cudaStream_t st) {
     if (L.nit <= 0 || L.jcount <= 0) return NB_OK;
     if (L.nit % kR4 != 0) return fail(NB_ERR_INVALID, "force: i-tile count %d not a multiple of %d", L.nit, kR4);
-    dim3 grid(L.nit, L.S), block(kNearThreads);
+    dim3 grid(L.nit * (kTJ / kNearOwner), L.S), block(kNearThreads);
     switch (force_method) {
         case kPairwise: force_near64_kernel<kPairwise><<<grid, block, 0, st>>>(pk, part, L); break;
         case kPlummer:  force_near64_kernel<kPlummer><<<grid, block, 0, st>>>(pk, part, L); break;

@@ -186,7 +186,7 @@ energy_partial_kernel(const double4* __restrict__ pos, const double4* __restrict
     if (threadIdx.x == 0) { double* o = red_part + (size_t)blockIdx.x * 4; o[0] = r[0]; o[1] = r[1]; o[2] = 0.0; o[3] = 0.0; }
 }
 __global__ void energy_final_kernel(const double* __restrict__ red, double* __restrict__ out3) {
-    const double kin = red[0], potl = -0.5 * kG * red[1];   // each unordered pair appears twice in sum_i m_i pot_i
+    const double kin = red[0], potl = -kG * red[1];   // potential_fp64_kernel gives every unordered pair a total weight of 1
     out3[0] = kin + potl; out3[1] = kin; out3[2] = potl;
 }
 

@@ -242,18 +242,34 @@ int render_splat(const double4* pos, const double4* vel, const unsigned int* per
                  const float color4[4], const float clear4[4], RenderState& st, float* range_out3, unsigned char* h_rgba,
                  cudaStream_t stream) {
     if (W <= 0 || H <= 0 || (long)W * H > (1L << 26)) return fail(NB_ERR_INVALID, "nb_render: image size %dx%d", W, H);
+    // Scratch that survives between frames: a render loop (nb_run_visualization) calls this once per frame between
+    // asynchronous steps, and a cudaMalloc / cudaFree pair per buffer would synchronise the device against them every time.
+    auto reserve = [&](int which, size_t bytes) -> int {
+        if (bytes <= st.cap[which]) return NB_OK;
+        NB_CUDA(cudaStreamSynchronize(stream));
+        cudaFree(st.buf[which]); st.buf[which] = nullptr; st.cap[which] = 0;
+        const size_t want = bytes + bytes / 4;                 // head room: fragment counts drift from frame to frame
+        NB_CUDA(cudaMalloc(&st.buf[which], want));
+        st.cap[which] = want;
+        return NB_OK;
+    };
+    auto up = [](size_t b) { return (b + 255) / 256 * 256; };
     // mass range once, max-speed EMA every call (ParticleRenderer.cpp:233-306)
     const int nb = (int)blocks_for(n);
-    float* d_part = nullptr; float* d_out = nullptr;
-    NB_CUDA(cudaMalloc(&d_part, (size_t)nb * 4 * sizeof(float) + 4 * sizeof(float)));
-    d_out = d_part + (size_t)nb * 4;
+    size_t scan_bytes = 0;
+    NB_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, (unsigned int*)nullptr, (unsigned long long*)nullptr, (int)n, stream));
+    const size_t b_part = up((size_t)nb * 4 * sizeof(float) + 4 * sizeof(float)), b_verts = up((size_t)n * sizeof(Vert)),
+                 b_counts = up((size_t)n * sizeof(unsigned int)), b_offs = up((size_t)(n + 1) * sizeof(unsigned long long)),
+                 b_img = up((size_t)W * H * 4), b_scan = up(scan_bytes ? scan_bytes : 16);
+    { int rc0 = reserve(0, b_part + b_verts + b_counts + b_offs + b_img + b_scan); if (rc0) return rc0; }
+    char* base0 = static_cast<char*>(st.buf[0]);
+    float* d_part = reinterpret_cast<float*>(base0);
+    float* d_out = d_part + (size_t)nb * 4;
     range_partial_kernel<<<nb, kThreads, 0, stream>>>(pos, vel, n, d_part);
     range_final_kernel<<<1, 1, 0, stream>>>(d_part, nb, d_out);
     float r3[4];
-    cudaError_t e = cudaMemcpyAsync(r3, d_out, sizeof(r3), cudaMemcpyDeviceToHost, stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    cudaFree(d_part);
-    NB_CUDA(e);
+    NB_CUDA(cudaMemcpyAsync(r3, d_out, sizeof(r3), cudaMemcpyDeviceToHost, stream));
+    NB_CUDA(cudaStreamSynchronize(stream));
     if (!st.have_mass) {
         if (r3[0] < r3[1]) { st.min_mass = r3[0]; st.max_mass = r3[1]; }
         else { st.min_mass = r3[0] < 3e38f ? r3[0] : 1.f; st.max_mass = st.min_mass * 10.0f; }      // :255-262 fallback
@@ -270,44 +286,40 @@ int render_splat(const double4* pos, const double4* vel, const unsigned int* per
     for (int k = 0; k < 4; ++k) { p.color[k] = color4[k]; p.clear[k] = clear4[k]; }
     if (range_out3) { range_out3[0] = p.min_mass; range_out3[1] = p.max_mass; range_out3[2] = p.max_velocity; range_out3[3] = p.scale; }
 
-    Vert* verts = nullptr; unsigned int* counts = nullptr; unsigned long long* offs = nullptr; void* tmp = nullptr;
-    unsigned long long *keys = nullptr, *keys2 = nullptr; float *al = nullptr, *al2 = nullptr; unsigned char* d_img = nullptr;
-    int rc = NB_OK;
-    auto cleanup = [&]() { cudaFree(verts); cudaFree(counts); cudaFree(offs); cudaFree(tmp); cudaFree(keys); cudaFree(keys2);
-                           cudaFree(al); cudaFree(al2); cudaFree(d_img); };
-#define NB_R(x) do { cudaError_t _e = (x); if (_e != cudaSuccess) { rc = cuda_fail(_e, #x, __FILE__, __LINE__); cleanup(); return rc; } } while (0)
-    NB_R(cudaMalloc(&verts, (size_t)n * sizeof(Vert)));
-    NB_R(cudaMalloc(&counts, (size_t)n * sizeof(unsigned int)));
-    NB_R(cudaMalloc(&offs, (size_t)(n + 1) * sizeof(unsigned long long)));
-    NB_R(cudaMalloc(&d_img, (size_t)W * H * 4));
+    Vert* verts = reinterpret_cast<Vert*>(base0 + b_part);
+    unsigned int* counts = reinterpret_cast<unsigned int*>(base0 + b_part + b_verts);
+    unsigned long long* offs = reinterpret_cast<unsigned long long*>(base0 + b_part + b_verts + b_counts);
+    unsigned char* d_img = reinterpret_cast<unsigned char*>(base0 + b_part + b_verts + b_counts + b_offs);
+    void* scan_tmp = base0 + b_part + b_verts + b_counts + b_offs + b_img;
     vertex_kernel<<<blocks_for(n), kThreads, 0, stream>>>(pos, vel, perm, n, p, verts, counts);
-    NB_R(cudaGetLastError());
-    size_t tb = 0;
-    NB_R(cub::DeviceScan::ExclusiveSum(nullptr, tb, counts, offs, (int)n, stream));
-    NB_R(cudaMalloc(&tmp, tb ? tb : 16));
-    NB_R(cub::DeviceScan::ExclusiveSum(tmp, tb, counts, offs, (int)n, stream));
+    NB_CUDA(cudaGetLastError());
+    size_t tb = b_scan;
+    NB_CUDA(cub::DeviceScan::ExclusiveSum(scan_tmp, tb, counts, offs, (int)n, stream));
     unsigned long long last_off = 0; unsigned int last_cnt = 0;
-    NB_R(cudaMemcpyAsync(&last_off, offs + (n - 1), sizeof(last_off), cudaMemcpyDeviceToHost, stream));
-    NB_R(cudaMemcpyAsync(&last_cnt, counts + (n - 1), sizeof(last_cnt), cudaMemcpyDeviceToHost, stream));
-    NB_R(cudaStreamSynchronize(stream));
+    NB_CUDA(cudaMemcpyAsync(&last_off, offs + (n - 1), sizeof(last_off), cudaMemcpyDeviceToHost, stream));
+    NB_CUDA(cudaMemcpyAsync(&last_cnt, counts + (n - 1), sizeof(last_cnt), cudaMemcpyDeviceToHost, stream));
+    NB_CUDA(cudaStreamSynchronize(stream));
     const unsigned long long nfrag = last_off + last_cnt;
-    if (nfrag > (1ULL << 30)) { cleanup(); return fail(NB_ERR_INVALID, "nb_render: %llu fragments (sprites too large for this image); reduce point_size", nfrag); }
+    if (nfrag > (1ULL << 30)) return fail(NB_ERR_INVALID, "nb_render: %llu fragments (sprites too large for this image); reduce point_size", nfrag);
+    unsigned long long *keys = nullptr, *keys2 = nullptr; float *al = nullptr, *al2 = nullptr;
     if (nfrag > 0) {
-        NB_R(cudaMalloc(&keys, nfrag * 8)); NB_R(cudaMalloc(&keys2, nfrag * 8));
-        NB_R(cudaMalloc(&al, nfrag * 4)); NB_R(cudaMalloc(&al2, nfrag * 4));
+        size_t sort_bytes = 0;
+        NB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys, keys2, al, al2, (int)nfrag, 0, 64, stream));
+        const size_t b_keys = up(nfrag * 8), b_al = up(nfrag * 4), b_sort = up(sort_bytes ? sort_bytes : 16);
+        { int rc1 = reserve(1, 2 * b_keys + 2 * b_al + b_sort); if (rc1) return rc1; }
+        char* base1 = static_cast<char*>(st.buf[1]);
+        keys = reinterpret_cast<unsigned long long*>(base1); keys2 = reinterpret_cast<unsigned long long*>(base1 + b_keys);
+        al = reinterpret_cast<float*>(base1 + 2 * b_keys); al2 = reinterpret_cast<float*>(base1 + 2 * b_keys + b_al);
+        void* sort_tmp = base1 + 2 * b_keys + 2 * b_al;
         fragment_kernel<<<blocks_for(n), kThreads, 0, stream>>>(verts, offs, n, W, keys, al);
-        NB_R(cudaGetLastError());
-        cudaFree(tmp); tmp = nullptr; tb = 0;
-        NB_R(cub::DeviceRadixSort::SortPairs(nullptr, tb, keys, keys2, al, al2, (int)nfrag, 0, 64, stream));
-        NB_R(cudaMalloc(&tmp, tb ? tb : 16));
-        NB_R(cub::DeviceRadixSort::SortPairs(tmp, tb, keys, keys2, al, al2, (int)nfrag, 0, 64, stream));
+        NB_CUDA(cudaGetLastError());
+        size_t sb = b_sort;
+        NB_CUDA(cub::DeviceRadixSort::SortPairs(sort_tmp, sb, keys, keys2, al, al2, (int)nfrag, 0, 64, stream));
     }
     resolve_kernel<<<blocks_for((long)W * H), kThreads, 0, stream>>>(keys2, al2, nfrag, verts, p, d_img);
-    NB_R(cudaGetLastError());
-    NB_R(cudaMemcpyAsync(h_rgba, d_img, (size_t)W * H * 4, cudaMemcpyDeviceToHost, stream));
-    NB_R(cudaStreamSynchronize(stream));
-#undef NB_R
-    cleanup();
+    NB_CUDA(cudaGetLastError());
+    NB_CUDA(cudaMemcpyAsync(h_rgba, d_img, (size_t)W * H * 4, cudaMemcpyDeviceToHost, stream));
+    NB_CUDA(cudaStreamSynchronize(stream));
     return NB_OK;
 }
 

@@ -41,6 +41,13 @@ with lib.context(n, prec, device=local) as ctx:
     e_mid = ctx.energy()                                  # collective: slice potentials + all-reduce; must not disturb the run
     ctx.step(0.04, 1)
     p_multi, v_multi = ctx.download()
+    # egress without the gather: every rank's own rows + their caller indices; together they must be the downloaded state
+    ps, vs, idx = ctx.download_slice()
+    full = torch.zeros((n, 8), dtype=torch.float64, device="cuda")
+    full[torch.from_numpy(idx.astype(np.int64)).cuda()] = torch.from_numpy(np.hstack([ps, vs])).cuda()
+    rows = torch.tensor([len(idx)], device="cuda")
+    dist.all_reduce(full); dist.all_reduce(rows)
+    slice_ok = int(rows.item()) == n and np.array_equal(full.cpu().numpy(), np.hstack([p_multi, v_multi]))
     mom = ctx.momentum()
     e_multi = ctx.energy()
     snap6 = np.zeros((n, 6)); sys2 = np.zeros(2); stat2 = np.zeros((n, 2))
@@ -56,7 +63,7 @@ with lib.context(n, prec, device=local) as ctx:          # the same thing on one
 err_a = nbtest.rel_err(a_multi, a_single).max()
 err_p = np.abs(p_multi[:, :3] - p_single[:, :3]).max()
 err_v = np.abs(v_multi[:, :3] - v_single[:, :3]).max()
-ok = err_a <= tol and err_p <= (1e-5 if prec == nbtest.FP32 else 1e-9) and err_v <= (1e-5 if prec == nbtest.FP32 else 1e-9)
+ok = slice_ok and err_a <= tol and err_p <= (1e-5 if prec == nbtest.FP32 else 1e-9) and err_v <= (1e-5 if prec == nbtest.FP32 else 1e-9)
 ok = ok and np.linalg.norm(mom[:3]) < 1e-6 * np.abs(pm[:, 3:4] * v[:, :3]).sum()
 # energy: FP64 in both precisions -> the sliced sum equals the single-GPU one to summation-order round-off of the state
 etol = 1e-6 if prec == nbtest.FP32 else 1e-11

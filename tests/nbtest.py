@@ -183,8 +183,10 @@ class Lib:
         l.nb_set_option.argtypes = [vp, C.c_char_p, C.c_long]
         l.nb_force_timing.argtypes = [vp, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
         l.nb_timer_start.argtypes = [vp]
-        l.nb_near_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
-        l.nb_get_order.argtypes = [vp, C.POINTER(C.c_uint)]
+        if os.environ.get("NB_LIB_PATH") is None or hasattr(l, "nb_download_slice"):      # an older build may be loaded for A/B timings
+            l.nb_near_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+            l.nb_get_order.argtypes = [vp, C.POINTER(C.c_uint)]
+            l.nb_download_slice.argtypes = [vp, _dp, _dp, C.POINTER(C.c_uint), C.c_long, C.POINTER(C.c_long)]
         l.nb_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
         l.nb_run_benchmark.argtypes = [C.c_long, _dp, _dp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
                                        C.c_int, C.c_int, C.c_int]
@@ -255,6 +257,16 @@ class Context:
         pm = np.zeros((self.n, 4)); v = np.zeros((self.n, 4))
         self.lib.check(self.l.nb_download(self.h, _p(pm), _p(v)))
         return pm, v
+
+    def download_slice(self, pm=None, v=None, index=None):
+        """Own rows only (multi-GPU egress without the gather): returns views of length count."""
+        cap = self.n if pm is None else pm.shape[0]
+        pm = np.zeros((cap, 4)) if pm is None else pm
+        v = np.zeros((cap, 4)) if v is None else v
+        index = np.zeros(cap, dtype=np.uint32) if index is None else index
+        cnt = C.c_long(0)
+        self.lib.check(self.l.nb_download_slice(self.h, _p(pm), _p(v), index.ctypes.data_as(C.POINTER(C.c_uint)), cap, C.byref(cnt)))
+        return pm[:cnt.value], v[:cnt.value], index[:cnt.value]
 
     def compute_accel(self):
         self.lib.check(self.l.nb_compute_accel(self.h))

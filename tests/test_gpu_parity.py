@@ -369,6 +369,21 @@ def test_step_graph_replay_is_bit_identical_to_plain_launches(lib, prec, integ):
     assert np.array_equal(states[0][2], states[1][2])
 
 
+def test_download_slice_on_one_gpu_is_the_whole_state(lib):
+    """nb_download_slice (multi-GPU egress without the gather) on a single device: all n rows in curve order + their indices."""
+    pm, v = nbtest.gen_spiral(5000, seed=4)
+    with lib.context(5000, FP32) as ctx:
+        ctx.upload(pm, v)
+        ctx.step(0.01, 2)
+        p, w = ctx.download()
+        ps, ws, idx = ctx.download_slice()
+        assert len(idx) == 5000 and np.array_equal(np.sort(idx), np.arange(5000))
+        assert np.array_equal(ps, p[idx]) and np.array_equal(ws, w[idx])
+        small = np.zeros((10, 4))
+        with pytest.raises(nbtest.NbError):
+            ctx.download_slice(small, small.copy(), np.zeros(10, dtype=np.uint32))
+
+
 def test_launch_force_on_caller_device_arrays(lib, oracle):
     """nb_launch_force (= launchForceKernel): caller-owned device double4 arrays, caller's stream."""
     import torch
