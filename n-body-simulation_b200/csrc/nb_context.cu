@@ -708,6 +708,9 @@ int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
         NB_NCCL(nccl::AllGather((const double*)(c->stage_pos + q * c->rank), (double*)c->stage_pos, (size_t)q * 4, nccl::kFloat64, c->comm, c->stream));
         NB_NCCL(nccl::AllGather((const double*)(c->stage_vel + q * c->rank), (double*)c->stage_vel, (size_t)q * 4, nccl::kFloat64, c->comm, c->stream));
     }
+    // Curve order and the gather into the master arrays need no mass statistics: enqueue them first, so that the device is
+    // busy (copy, all-gather, key sort) while the host walks the masses.
+    rc = ingest(c, c->stage_pos, c->stage_vel); if (rc) return rc;
     // computeAverageMass (core/Forces.cpp:85-95): serial sum in index order on the host, exactly as the reference.
     double total = 0.0;
     long bad = -1;
@@ -716,10 +719,10 @@ int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
     // accelerations for everybody. The reference's arithmetic accepts such input; FP64 mode here does too.
     if (bad >= 0 && c->precision == NB_PREC_FP32) {
         NB_CUDA(cudaStreamSynchronize(c->stream));
+        c->uploaded = false; c->have_accel = false;
         return fail(NB_ERR_INVALID, "nb_upload: particle %ld has mass %g; FP32 mode needs masses >= 0 (use NB_PREC_FP64)", bad, posMass4[4 * bad + 3]);
     }
     c->avg_mass = total / (double)c->n;
-    rc = ingest(c, c->stage_pos, c->stage_vel); if (rc) return rc;
     StepArrays A = arrays(c);
     rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream); if (rc) return rc;
     c->launches++;
