@@ -125,7 +125,9 @@ def ncu_traffic_bytes(spec, world):
             tot = 0.0
             for line in open(path):
                 if line.startswith("dram__bytes_read.sum [Mbyte]") or line.startswith("dram__bytes_write.sum [Mbyte]"):
-                    tot += float(line.split("=")[1]) * 1e6
+                    v = float(line.split("=")[1])
+                    if v == v:                      # ncu reports nan for kernels whose counters it could not collect
+                        tot += v * 1e6
             if tot:
                 return tot, "profiles/" + name
         except OSError:
@@ -285,7 +287,7 @@ def roofline_for(spec, n_sm, f_max, peak_src, rates, per_gpu_interactions, fk_ms
     r["peak_Tint_per_s"] = peak / 1e12
     r["traffic"], traffic_src = ncu_traffic_bytes(spec, world)
     if r["traffic"]:
-        r["traffic_note"] = (f"DRAM bytes per force evaluation (far + near kernel) from {traffic_src}; algorithmic: packed tiles "
+        r["traffic_note"] = (f"DRAM bytes per force evaluation from {traffic_src} (far kernel; ncu returned no DRAM counters for the near kernel at this grid size — its 32 partial slots add about 0.8 GB); algorithmic: packed tiles "
                              f"({40 * spec['n'] / 1e6:.0f} MB, re-read from L2 by every CTA) + result ({24 * spec['n'] / 1e6:.0f} MB); the rest is "
                              "the partial-sum slots of the fixed-order reduction, written once and read once")
     r["peak_source"] = (f"{n_sm} SMs x sm_max_mhz from {peak_src}; pipe rates (warp-instr/clk/SM) ffma {rates['ffma']:.3f} ffma2 "

@@ -731,7 +731,8 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
     __shared__ __align__(16) double Js[4][kSubTile];                   // x', y', z' (owner frame), G m of the staged sub-tile
     __shared__ float Mqs[kSubTile];
     __shared__ int list[kNearThreads];                                 // near tiles of the current round of 256, in order
-    __shared__ int wcount[kNearThreads / 32];
+    __shared__ int wcount[kNearThreads / 32], wcount2[kNearThreads / 32];
+    __shared__ int items[4 * kNearThreads];                            // (tile << 2) | sub-tile of the round's near items, in order
     __shared__ double red[3][kNearOwner];
     const int t = threadIdx.x, lane = t & 31, w = t >> 5, s = blockIdx.y;
     const int il = t & (kNearOwner - 1), jh = t / kNearOwner;           // my i-particle, my half of every sub-tile
@@ -751,7 +752,7 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
     const double mqi = IS_ADAPTIVE(MODE) ? (double)q[7 * kTJ] : 0.0;
     double ax = 0.0, ay = 0.0, az = 0.0;
     for (int base = k0; base < k1; base += kNearThreads) {
-        // 256 tiles per round against the far kernel's CTA box (its first-level test); ordered compaction of the survivors
+        // Level 1: 256 tiles per round against the far kernel's CTA box (its first-level test); ordered compaction.
         const int kk = base + t;
         bool refine = false;
         if (kk < k1) {
@@ -766,44 +767,74 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
         for (int v = 0; v < kNearThreads / 32; ++v) { const int c = wcount[v]; if (v < w) before += c; total += c; }
         if (refine) list[before + __popc(bal & ((1u << lane) - 1u))] = kk;
         __syncthreads();
-        for (int e = 0; e < total; ++e) {
-            const float* tile = pk + (size_t)wrap_tile(L.jt0 + list[e], L.ntiles) * kTileFloats;
-            const float* meta = tile + kMetaRow * kTJ;
-#pragma unroll 1
+        // Level 2: thread e tests the four sub-tile boxes of surviving tile e against the owner's box — all tiles of the round
+        // at once, so the meta rows arrive with one memory latency instead of one per tile; ordered compaction into items.
+        int mask = 0, mytile = 0;
+        if (t < total) {
+            mytile = list[t];
+            const float* meta = pk + (size_t)wrap_tile(L.jt0 + mytile, L.ntiles) * kTileFloats + kMetaRow * kTJ;
+#pragma unroll
             for (int sb = 0; sb < kTJ / kSubTile; ++sb) {
                 const float* sbox = meta + kSubBoxOffset + 6 * sb;
-                if (boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) continue;      // far kernel, warp frame (CTA-uniform)
-                __syncthreads();                                                             // the previous sub-tile is done with
-                if (t < kSubTile) {
-                    const float* pj = tile + sb * kSubTile + t;
-                    Js[0][t] = ((double)pj[0 * kTJ] - (double)Ow[0]) + (double)pj[4 * kTJ];
-                    Js[1][t] = ((double)pj[1 * kTJ] - (double)Ow[1]) + (double)pj[5 * kTJ];
-                    Js[2][t] = ((double)pj[2 * kTJ] - (double)Ow[2]) + (double)pj[6 * kTJ];
-                    Js[3][t] = (double)pj[3 * kTJ] + (double)pj[kGmLoRow * kTJ];
-                    if (IS_ADAPTIVE(MODE)) Mqs[t] = pj[7 * kTJ];
-                }
-                __syncthreads();
-                // the interactions of one sub-tile are summed on their own and then added to the running sums
-                double sx = 0.0, sy = 0.0, sz = 0.0;
-                const int j0 = jh * (kSubTile / 2);
-#pragma unroll 4
-                for (int j = j0; j < j0 + kSubTile / 2; ++j) {
-                    const double dx = Js[0][j] - xi, dy = Js[1][j] - yi, dz = Js[2][j] - zi, gm = Js[3][j];
-                    const double r2 = dx * dx + dy * dy + dz * dz;
-                    double s2 = r2;
-                    if (IS_ADAPTIVE(MODE)) {
-                        const double wq = pow23(mqi + (double)Mqs[j]);
-                        s2 = fmax(fma(r2 * wq, 1e-4, r2), r2 + 1e-8);
-                    }
-                    if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
-                    double sc = gm_inv_r3(s2, gm);
-                    if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
-                    sx = fma(sc, dx, sx); sy = fma(sc, dy, sy); sz = fma(sc, dz, sz);
-                }
-                ax += sx; ay += sy; az += sz;
+                if (!boxes_far(Wbox, Hw, sbox, sbox + 3, L.kappa, min_gap2)) mask |= 1 << sb;      // else: far kernel, warp frame
             }
         }
-        __syncthreads();                                                                     // list / wcount are rewritten next round
+        const int cnt = __popc(mask);
+        int incl = cnt;                                    // inclusive prefix sum over the warp
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += v; }
+        if (lane == 31) wcount2[w] = incl;
+        __syncthreads();
+        int ibefore = 0, n_items = 0;
+#pragma unroll
+        for (int v = 0; v < kNearThreads / 32; ++v) { const int c = wcount2[v]; if (v < w) ibefore += c; n_items += c; }
+        {
+            int pos = ibefore + incl - cnt;
+#pragma unroll
+            for (int sb = 0; sb < kTJ / kSubTile; ++sb) if (mask & (1 << sb)) items[pos++] = (mytile << 2) | sb;
+        }
+        __syncthreads();
+        // Items one after the other; the j-particles of item e+1 are fetched into registers while item e is computed.
+        float pre[9];
+        auto prefetch = [&](int e) {
+            const int it = items[e];
+            const float* pj = pk + (size_t)wrap_tile(L.jt0 + (it >> 2), L.ntiles) * kTileFloats + (it & 3) * kSubTile + t;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) pre[c] = pj[c * kTJ];
+            pre[8] = pj[kGmLoRow * kTJ];
+        };
+        if (n_items > 0 && t < kSubTile) prefetch(0);
+        for (int e = 0; e < n_items; ++e) {
+            __syncthreads();                                                                 // the previous item is done with
+            if (t < kSubTile) {
+                Js[0][t] = ((double)pre[0] - (double)Ow[0]) + (double)pre[4];
+                Js[1][t] = ((double)pre[1] - (double)Ow[1]) + (double)pre[5];
+                Js[2][t] = ((double)pre[2] - (double)Ow[2]) + (double)pre[6];
+                Js[3][t] = (double)pre[3] + (double)pre[8];
+                if (IS_ADAPTIVE(MODE)) Mqs[t] = pre[7];
+            }
+            __syncthreads();
+            if (e + 1 < n_items && t < kSubTile) prefetch(e + 1);
+            // the interactions of one sub-tile are summed on their own and then added to the running sums
+            double sx = 0.0, sy = 0.0, sz = 0.0;
+            const int j0 = jh * (kSubTile / 2);
+#pragma unroll 4
+            for (int j = j0; j < j0 + kSubTile / 2; ++j) {
+                const double dx = Js[0][j] - xi, dy = Js[1][j] - yi, dz = Js[2][j] - zi, gm = Js[3][j];
+                const double r2 = dx * dx + dy * dy + dz * dz;
+                double s2 = r2;
+                if (IS_ADAPTIVE(MODE)) {
+                    const double wq = pow23(mqi + (double)Mqs[j]);
+                    s2 = fmax(fma(r2 * wq, 1e-4, r2), r2 + 1e-8);
+                }
+                if (IS_PLUMMER(MODE)) s2 = r2 + 1e-10;                                          // cuda/ForceKernels.cu:186
+                double sc = gm_inv_r3(s2, gm);
+                if (!IS_PLUMMER(MODE)) sc = (__double_as_longlong(r2) < __double_as_longlong(kR2Cut)) ? 0.0 : sc;   // cut-off, self pair
+                sx = fma(sc, dx, sx); sy = fma(sc, dy, sy); sz = fma(sc, dz, sz);
+            }
+            ax += sx; ay += sy; az += sz;
+        }
+        __syncthreads();                                                                     // list / items are rewritten next round
     }
     if (jh == 1) { red[0][il] = ax; red[1][il] = ay; red[2][il] = az; }
     __syncthreads();
