@@ -76,6 +76,14 @@ int nb_comm_init(nb_ctx* ctx, const void* id128, int rank, int world);
  * FP32-mode contexts return NB_ERR_INVALID for a negative or NaN mass (the far field works in a mass-scaled frame);
  * FP64-mode contexts take any mass, like the reference's arithmetic. */
 int nb_upload(nb_ctx* ctx, const double* posMass4, const double* vel4);
+/* SPIRAL_GALAXY initial conditions made on the device instead of nb_upload (Initializer::initSpiralGalaxy,
+ * core/Initializer.cpp:360-469: same distribution, formulas and parameters — total mass, arms, radius, thickness, velocity
+ * perturbation — as the reference generator). Every draw is a function of (seed, particle index, draw number), so the result
+ * does not depend on the number of GPUs or threads; it is NOT the std::mt19937 sequence of the host generator. Particle i of
+ * the caller's order is what nb_download returns in row i. normal3 (may be NULL) receives the disc's unit normal.
+ * Multi-GPU: every rank calls it with the same arguments. */
+int nb_init_spiral(nb_ctx* ctx, unsigned long long seed, double total_mass, int arms, double radius, double thickness,
+                   double perturbation, double* normal3);
 /* Device -> host of the final state (cuda/BenchmarkKernels.cu:101-102), all n rows, caller order. Multi-GPU: collective
  * (the slices are all-gathered first), every rank receives the complete state. */
 int nb_download(nb_ctx* ctx, double* posMass4, double* vel4);
@@ -157,6 +165,7 @@ int nb_timer_stop(nb_ctx* ctx, float* ms);
  *                      | 2 bulk-copy (TMA) tiles in the i-block's frame, 2 i-particles/thread, FP32 two-float near field
  *                      | 3 as 2 with 4 i-particles/thread and the near field (adjacent tiles) in FP64 (production)
  *   "j_splits"         0 auto | 1..64 CTAs sharing one i-block's j-range
+ *   "near_splits"      0 auto | 1..64 j-splits of the FP64 near-field kernel (FP32 mode)
  *   "spatial_sort"     1 (default) order the particles along a 3-D Hilbert curve at upload | 2 Morton (Z) curve
  *                      | 0 keep the caller's order
  *   "collect_stats"    1 = count tile classifications (see nb_tile_stats); costs a few atomics per tile

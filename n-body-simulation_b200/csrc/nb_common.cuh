@@ -89,6 +89,8 @@ int launch_accel_export(const double* acc, long npad, long first, long count, do
 int launch_accel_import_sum(const double* part, int S, long npad, long n, double4* out, cudaStream_t st);
 int launch_mass_sum(const double4* pos, long n, double* red_part, double* red, cudaStream_t st);
 int launch_momentum(const double4* pos, const double4* vel, long first, long count, double* red_part, double* red, cudaStream_t st);
+int launch_spiral_init(unsigned long long seed, long n, double total_mass, int arms, double radius, double thickness,
+                       double perturbation, double4* pos, double4* vel, double* normal3, cudaStream_t st);
 
 // nb_sort.cu
 struct SortScratch {

@@ -94,7 +94,7 @@ struct nb_ctx {
     bool uploaded = false, have_accel = false, force_timed = false;
     nccl::comm_t comm = nullptr;
     long launches = 0;
-    int force_variant = 0, j_splits = 0;
+    int force_variant = 0, j_splits = 0, near_splits = 0;
     // Small systems: one captured step (drift, FP64 force, finish, COM) replayed as a CUDA graph — see step_graph_for().
     bool step_graph_enabled = false; cudaGraphExec_t step_graph = nullptr;
     struct StepKey { double dt = 0, avg_mass = 0; int integ = -1, force = -1, sub = -1, S = 0; const void* part = nullptr; } step_key;
@@ -252,6 +252,7 @@ int eval_force(nb_ctx* c, int* S_out) {
         if (want > 64) want = 64;
         if (want > c->ntiles / 2) want = c->ntiles / 2;
         S_near = want < 1 ? 1 : (int)want;
+        if (c->near_splits > 0) S_near = c->near_splits < c->ntiles ? c->near_splits : c->ntiles;
     }
     if (c->world == 1) {
         L.jt0 = 0; L.jcount = c->ntiles; L.s0 = 0; L.S = splits_for(c, iblocks, L.jcount);
@@ -637,6 +638,7 @@ int nb_set_methods(nb_ctx* c, int integ, int force, int subtract_com) {
 int nb_set_option(nb_ctx* c, const char* key, long value) {
     if (!c || !key) return fail(NB_ERR_INVALID, "nb_set_option: NULL argument");
     if (!strcmp(key, "force_variant")) { if (value < 0 || value > 3) return fail(NB_ERR_INVALID, "force_variant must be 0..3"); c->force_variant = (int)value; return NB_OK; }
+    if (!strcmp(key, "near_splits")) { if (value < 0 || value > 64) return fail(NB_ERR_INVALID, "near_splits must be 0..64"); c->near_splits = (int)value; return NB_OK; }
     if (!strcmp(key, "j_splits")) { if (value < 0 || value > 64) return fail(NB_ERR_INVALID, "j_splits must be 0..64"); c->j_splits = (int)value; return NB_OK; }
     if (!strcmp(key, "spatial_sort")) { if (value < 0 || value > 2) return fail(NB_ERR_INVALID, "spatial_sort must be 0..2"); c->spatial_sort = (int)value; return NB_OK; }
     if (!strcmp(key, "collect_stats")) {
@@ -728,6 +730,27 @@ int nb_upload(nb_ctx* c, const double* posMass4, const double* vel4) {
     c->launches++;
     c->uploaded = true; c->have_accel = false; c->steps_since_sort = 0;
     NB_CUDA(cudaStreamSynchronize(c->stream));      // the host buffers may be reused as soon as we return
+    return NB_OK;
+}
+
+int nb_init_spiral(nb_ctx* c, unsigned long long seed, double total_mass, int arms, double radius, double thickness,
+                   double perturbation, double* normal3) {
+    if (!c) return fail(NB_ERR_INVALID, "nb_init_spiral: ctx is NULL");
+    int rc = use_device(c); if (rc) return rc;
+    // every rank generates the whole system (O(N), identical on every device by construction); no host arrays, no H2D
+    rc = launch_spiral_init(seed, c->n, total_mass, arms, radius, thickness, perturbation, c->stage_pos, c->stage_vel, normal3, c->stream);
+    if (rc) return rc;
+    rc = ingest(c, c->stage_pos, c->stage_vel); if (rc) return rc;
+    // computeAverageMass (core/Forces.cpp:85-95) of n equal masses, summed one by one like the reference does
+    const double m = total_mass / (double)c->n;
+    double total = 0.0;
+    for (long i = 0; i < c->n; ++i) total += m;
+    c->avg_mass = total / (double)c->n;
+    StepArrays A = arrays(c);
+    rc = launch_pack(A, 0, c->npad, c->avg_mass, c->stream); if (rc) return rc;
+    c->launches += 2;
+    c->uploaded = true; c->have_accel = false; c->steps_since_sort = 0;
+    NB_CUDA(cudaStreamSynchronize(c->stream));
     return NB_OK;
 }
 

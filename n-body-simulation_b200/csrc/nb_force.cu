@@ -854,10 +854,20 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
 #ifndef NB_FP64_UNROLL4
 #define NB_FP64_UNROLL4 4
 #endif
+#ifndef NB_FP64_UNROLL2
+#define NB_FP64_UNROLL2 4
+#endif
+#ifndef NB_FP64_BIG_R
+#define NB_FP64_BIG_R 4
+#endif
+constexpr int kFp64Unroll2 = NB_FP64_UNROLL2;
 constexpr int kFp64Unroll4 = NB_FP64_UNROLL4;      // j-particles per iteration of the inner loop with 4 i-particles per thread
 
+#ifndef NB_FP64_MINB
+#define NB_FP64_MINB 2
+#endif
 template <int MODE, int R>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, NB_FP64_MINB)
 force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, const ForceLaunch L, double inv3mbar) {
     __shared__ __align__(16) double4 sm[2][kTJ];
     __shared__ double smq[IS_ADAPTIVE(MODE) ? 2 : 1][IS_ADAPTIVE(MODE) ? kTJ : 1];
@@ -885,7 +895,7 @@ force_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ part, co
         double tx[R], ty[R], tz[R];
 #pragma unroll
         for (int r = 0; r < R; ++r) tx[r] = ty[r] = tz[r] = 0.0;
-#pragma unroll (R >= 4 ? kFp64Unroll4 : 4)
+#pragma unroll (R >= 4 ? kFp64Unroll4 : kFp64Unroll2)
         for (int j = 0; j < kTJ; ++j) {
             const double4 pj = sm[b][j];                       // (x, y, z, G m)
             const double mqj = IS_ADAPTIVE(MODE) ? smq[IS_ADAPTIVE(MODE) ? b : 0][IS_ADAPTIVE(MODE) ? j : 0] : 0.0;
@@ -1061,7 +1071,7 @@ int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, int f
 
 // i-particles per thread of the FP64 kernel: 4 once the system fills the GPU (PAIRWISE: +5 %), 2 for small systems (more,
 // shorter CTAs) and for ADAPTIVE_MUTUAL (4 leave too few registers for the q^(2/3) arithmetic: -5.5 %)
-int force_fp64_i_tiles(long npad, int force_method) { return (npad >= 32768 && force_method != kAdaptive) ? 4 : 2; }
+int force_fp64_i_tiles(long npad, int force_method) { return (npad >= 32768 && force_method != kAdaptive) ? NB_FP64_BIG_R : 2; }
 
 template <int R>
 static int launch_force_fp64_r(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st) {

@@ -333,4 +333,71 @@ int launch_momentum(const double4* pos, const double4* vel, long first, long cou
     return NB_OK;
 }
 
+// ---- device-side SPIRAL_GALAXY generator (core/Initializer.cpp:360-469) -------------------------------------------------
+// Same distribution and the same formulas as the reference generator (equal-mass stars, uniform-area disc r = R sqrt(u), arm
+// by index, random in-arm angle, uniform thickness, rotation curve v = v0 sqrt(r/R) plus a uniform velocity perturbation, random
+// disc orientation), but every draw is a pure function of (seed, particle index, draw number) — a counter-based generator
+// (splitmix64 finaliser) instead of one sequential std::mt19937 stream — so that the particles can be made where they are
+// needed: on the device, by any number of threads or GPUs, identically. 16M particles take a fraction of a millisecond
+// instead of seconds on the host plus 1 GB over PCIe.
+__host__ __device__ inline unsigned long long nb_mix64(unsigned long long z) {
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+// uniform in [0, 1) with 53 random bits: draw k of particle i (i = 2^63 - 1: the per-system draws)
+__host__ __device__ inline double nb_u01(unsigned long long seed, unsigned long long i, unsigned k) {
+    return (double)(nb_mix64(nb_mix64(seed) ^ nb_mix64(i * 8ULL + k)) >> 11) * (1.0 / 9007199254740992.0);
+}
+
+struct SpiralParams { double mass, radius, thickness, perturbation, v0; int arms; double e1[3], e2[3], nrm[3]; };
+
+__global__ void __launch_bounds__(kThreads)
+spiral_init_kernel(unsigned long long seed, long n, SpiralParams P, double4* __restrict__ pos, double4* __restrict__ vel) {
+    const long i = (long)blockIdx.x * kThreads + threadIdx.x;
+    if (i >= n) return;
+    const double kPi = 3.14159265358979323846;
+    const double u = nb_u01(seed, i, 0);
+    const double r = P.radius * sqrt(u);
+    const double phi = (2.0 * kPi * (double)(i % P.arms)) / (double)P.arms + (r / P.radius) * 2.0 * kPi +
+                       (nb_u01(seed, i, 1) * 2.0 - 1.0) * (kPi / 8.0);
+    double sphi, cphi; sincos(phi, &sphi, &cphi);
+    const double xd = r * cphi, yd = r * sphi, zd = (nb_u01(seed, i, 2) - 0.5) * P.thickness;
+    const double sp = P.v0 * sqrt(r / P.radius);
+    double x[3], v[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        x[c] = xd * P.e1[c] + yd * P.e2[c] + zd * P.nrm[c];
+        v[c] = sp * (-sphi * P.e1[c] + cphi * P.e2[c]) + (nb_u01(seed, i, 3 + c) * 2.0 - 1.0) * P.perturbation;
+    }
+    pos[i] = make_double4(x[0], x[1], x[2], P.mass);
+    vel[i] = make_double4(v[0], v[1], v[2], 0.0);
+}
+
+int launch_spiral_init(unsigned long long seed, long n, double total_mass, int arms, double radius, double thickness,
+                       double perturbation, double4* pos, double4* vel, double* normal3, cudaStream_t st) {
+    if (n <= 0 || arms <= 0 || !(radius > 0.0) || !(total_mass > 0.0))
+        return fail(NB_ERR_INVALID, "spiral generator: n=%ld arms=%d radius=%g total mass=%g", n, arms, radius, total_mass);
+    SpiralParams P;
+    P.mass = total_mass / (double)n; P.radius = radius; P.thickness = thickness; P.perturbation = perturbation; P.arms = arms;
+    P.v0 = sqrt(kG * total_mass / radius);
+    const double kPi = 3.14159265358979323846;
+    const unsigned long long sys = 0x7FFFFFFFFFFFFFFFULL;                  // the two per-system draws: disc orientation
+    const double th = nb_u01(seed, sys, 0) * kPi, ph = nb_u01(seed, sys, 1) * 2.0 * kPi;
+    P.nrm[0] = sin(th) * cos(ph); P.nrm[1] = sin(th) * sin(ph); P.nrm[2] = cos(th);
+    if (fabs(P.nrm[0]) < 1e-6 && fabs(P.nrm[1]) < 1e-6) { P.e1[0] = 1; P.e1[1] = 0; P.e1[2] = 0; }
+    else {
+        const double len = sqrt(P.nrm[0] * P.nrm[0] + P.nrm[1] * P.nrm[1]);
+        P.e1[0] = -P.nrm[1] / len; P.e1[1] = P.nrm[0] / len; P.e1[2] = 0.0;
+    }
+    P.e2[0] = P.nrm[1] * P.e1[2] - P.nrm[2] * P.e1[1];
+    P.e2[1] = P.nrm[2] * P.e1[0] - P.nrm[0] * P.e1[2];
+    P.e2[2] = P.nrm[0] * P.e1[1] - P.nrm[1] * P.e1[0];
+    if (normal3) { normal3[0] = P.nrm[0]; normal3[1] = P.nrm[1]; normal3[2] = P.nrm[2]; }
+    spiral_init_kernel<<<blocks_for(n), kThreads, 0, st>>>(seed, n, P, pos, vel);
+    NB_CUDA(cudaGetLastError());
+    return NB_OK;
+}
+
 } // namespace nb

@@ -58,6 +58,7 @@ Config parse_config_text(const std::string& text) {
     if (j.contains("subtractCom")) c.subtractCom = j["subtractCom"].as_bool();
     if (j.contains("device")) c.device = j["device"].as_int();
     if (j.contains("snapshotOut")) c.snapshotOut = j["snapshotOut"].as_string();
+    if (j.contains("deviceInit")) c.deviceInit = j["deviceInit"].as_bool();
     if (j.contains("frames")) {
         const Json& f = j["frames"];
         c.hasFrames = true;
@@ -384,6 +385,42 @@ const char* name_of(OutputMode o) {
 }
 } // namespace
 
+// "deviceInit": true — SPIRAL_GALAXY initial conditions made on the GPU (nb_init_spiral: the reference generator's formulas with
+// counter-based draws), BENCHMARK mode: nothing but the final state ever crosses PCIe. What a 16M-particle run wants: the host
+// generator takes seconds and 1 GB of upload there.
+static RunReport run_device_init(const Config& cfg, long steps, bool quiet) {
+    if (cfg.initSelected != "SPIRAL_GALAXY" || cfg.outputMode != OutputMode::BENCHMARK || !cfg.hasSeed)
+        throw std::runtime_error("\"deviceInit\": true needs initializationMethod SPIRAL_GALAXY, outputMode BENCHMARK and a \"seed\"");
+    RunReport rep;
+    const Json& q = cfg.initParams;
+    const long n = q["nStars"].as_int();
+    ParticleSet p((size_t)n);
+    const int prec = cfg.precision >= 0 ? cfg.precision : NB_PREC_FP32;
+    nb_ctx* c = nullptr;
+    auto t0 = std::chrono::high_resolution_clock::now();
+    check(nb_create(&c, n, cfg.device, prec));
+    double nrm[3] = {0, 0, 0};
+    int rc = nb_set_methods(c, (int)cfg.integrationMethod, (int)cfg.forceMethod, cfg.subtractCom ? 1 : 0);
+    if (!rc) rc = nb_init_spiral(c, (unsigned long long)cfg.seed, q["totalMass"].as_double(), q["nArms"].as_int(), q["galaxyRadius"].as_double(),
+                                 q["thickness"].as_double(), q["perturbation"].as_double(), nrm);
+    auto t1 = std::chrono::high_resolution_clock::now();
+    if (!rc) rc = nb_compute_accel(c);
+    if (!rc) rc = nb_step(c, cfg.dtYears, (int)steps);
+    if (!rc) rc = nb_download(c, p.posMass.data(), p.vel.data());
+    auto t2 = std::chrono::high_resolution_clock::now();
+    nb_destroy(c);
+    check(rc);
+    rep.init_seconds = std::chrono::duration<double>(t1 - t0).count();
+    rep.run_seconds = std::chrono::duration<double>(t2 - t1).count();
+    rep.steps = steps; rep.n = (size_t)n;
+    if (!quiet)
+        std::cout << "Initialization time: " << rep.init_seconds << " seconds (on the device; disc normal " << nrm[0] << ", " << nrm[1] << ", "
+                  << nrm[2] << ")\nInitialization mode: SPIRAL_GALAXY\nForce method: " << name_of(cfg.forceMethod)
+                  << "\nExecution mode: GPU\nOutput mode: BENCHMARK\n";
+    if (!cfg.snapshotOut.empty()) save_snapshot(cfg.snapshotOut, p);
+    return rep;
+}
+
 // The flow of the reference's main (core/main.cpp:454-636) + System::runSimulation (core/System.cpp:87-157) for
 // executionMode "GPU": BENCHMARK -> nb_run_benchmark, FILE_CSV -> nb_run_simulation + write_csv.
 RunReport run_config(const Config& cfg, bool quiet) {
@@ -395,6 +432,7 @@ RunReport run_config(const Config& cfg, bool quiet) {
                                  "this machine); add a \"frames\" object to the config for headless PPM frames of the same shader arithmetic");
     const long steps = (long)(cfg.years / cfg.dtYears);                 // main.cpp:496
     const long stepFreq = std::max(1L, steps / 500);                    // main.cpp:499,525
+    if (cfg.deviceInit) return run_device_init(cfg, steps, quiet);
     auto t0 = std::chrono::high_resolution_clock::now();
     InitResult init = create_initial_conditions(cfg);
     auto t1 = std::chrono::high_resolution_clock::now();

@@ -57,6 +57,7 @@ struct Config {
     bool subtractCom = true;
     int device = -1;
     std::string snapshotOut;
+    bool deviceInit = false;       // SPIRAL_GALAXY + BENCHMARK: initial conditions generated on the GPU (nb_init_spiral), needs "seed"
     bool hasFrames = false; std::string frameDir = "frames"; int frameWidth = 1280, frameHeight = 720;   // VisualizationUtils.cpp:15-16
     int physicsStepsPerFrame = 0, frameEvery = 0; double frameScale = 0.0;
 };

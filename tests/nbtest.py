@@ -187,6 +187,7 @@ class Lib:
             l.nb_near_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_int)]
             l.nb_get_order.argtypes = [vp, C.POINTER(C.c_uint)]
             l.nb_download_slice.argtypes = [vp, _dp, _dp, C.POINTER(C.c_uint), C.c_long, C.POINTER(C.c_long)]
+            l.nb_init_spiral.argtypes = [vp, C.c_ulonglong, C.c_double, C.c_int, C.c_double, C.c_double, C.c_double, _dp]
         l.nb_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
         l.nb_run_benchmark.argtypes = [C.c_long, _dp, _dp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int,
                                        C.c_int, C.c_int, C.c_int]
@@ -267,6 +268,11 @@ class Context:
         cnt = C.c_long(0)
         self.lib.check(self.l.nb_download_slice(self.h, _p(pm), _p(v), index.ctypes.data_as(C.POINTER(C.c_uint)), cap, C.byref(cnt)))
         return pm[:cnt.value], v[:cnt.value], index[:cnt.value]
+
+    def init_spiral(self, seed, total_mass=1e4, arms=2, radius=3.09398e3, thickness=6.18795e2, perturbation=5.0):
+        nrm = np.zeros(3)
+        self.lib.check(self.l.nb_init_spiral(self.h, seed, total_mass, arms, radius, thickness, perturbation, _p(nrm)))
+        return nrm
 
     def compute_accel(self):
         self.lib.check(self.l.nb_compute_accel(self.h))
@@ -401,3 +407,38 @@ def rel_err(a, b):
     nb = np.linalg.norm(b, axis=1)
     d = np.linalg.norm(a - b, axis=1)
     return np.where(nb > 0, d / np.where(nb > 0, nb, 1.0), d)
+
+
+def _mix64(z):
+    z = (z + np.uint64(0x9E3779B97F4A7C15))
+    z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+    z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+    return z ^ (z >> np.uint64(31))
+
+
+def _u01(seed, i, k):
+    with np.errstate(over="ignore"):
+        s = _mix64(np.uint64(seed))
+        h = _mix64(s ^ _mix64(np.asarray(i, dtype=np.uint64) * np.uint64(8) + np.uint64(k)))
+    return (h >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def gen_spiral_counter(n, seed, total_mass=1e4, arms=2, radius=3.09398e3, thickness=6.18795e2, perturbation=5.0):
+    """numpy restatement of nb_init_spiral (csrc/nb_integrate.cu: counter-based draws, the reference's formulas of
+    core/Initializer.cpp:360-469): the checker of the device-side generator."""
+    sysid = np.uint64(0x7FFFFFFFFFFFFFFF)
+    th, ph = float(_u01(seed, sysid, 0)) * np.pi, float(_u01(seed, sysid, 1)) * 2 * np.pi
+    nrm = np.array([np.sin(th) * np.cos(ph), np.sin(th) * np.sin(ph), np.cos(th)])
+    e1 = np.array([-nrm[1], nrm[0], 0.0]) / np.hypot(nrm[0], nrm[1])
+    e2 = np.cross(nrm, e1)
+    i = np.arange(n, dtype=np.uint64)
+    r = radius * np.sqrt(_u01(seed, i, 0))
+    phi = 2 * np.pi * (np.arange(n) % arms) / arms + r / radius * 2 * np.pi + (_u01(seed, i, 1) * 2 - 1) * (np.pi / 8)
+    xd, yd, zd = r * np.cos(phi), r * np.sin(phi), (_u01(seed, i, 2) - 0.5) * thickness
+    sp = np.sqrt(G * total_mass / radius) * np.sqrt(r / radius)
+    pm = np.zeros((n, 4)); v = np.zeros((n, 4))
+    pm[:, :3] = xd[:, None] * e1 + yd[:, None] * e2 + zd[:, None] * nrm
+    pm[:, 3] = total_mass / n
+    pert = np.stack([_u01(seed, i, 3 + c) * 2 - 1 for c in range(3)], axis=1) * perturbation
+    v[:, :3] = sp[:, None] * ((-np.sin(phi))[:, None] * e1 + np.cos(phi)[:, None] * e2) + pert
+    return pm, v, nrm

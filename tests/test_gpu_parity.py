@@ -369,6 +369,28 @@ def test_step_graph_replay_is_bit_identical_to_plain_launches(lib, prec, integ):
     assert np.array_equal(states[0][2], states[1][2])
 
 
+def test_device_side_spiral_generator(lib, oracle):
+    """nb_init_spiral: the state made on the device equals the numpy restatement of the same counter-based draws (to the last
+    bits of sin/cos/sqrt), in the caller's index order, and the context is ready to step from it."""
+    n = 50000
+    pm, v, nrm = nbtest.gen_spiral_counter(n, seed=12345)
+    with lib.context(n, FP64) as ctx:
+        got_nrm = ctx.init_spiral(12345)
+        p, w = ctx.download()
+        assert np.allclose(got_nrm, nrm, rtol=0, atol=1e-15)
+        assert np.array_equal(p[:, 3], pm[:, 3]) and np.all(w[:, 3] == 0.0)
+        assert np.abs(p[:, :3] - pm[:, :3]).max() <= 1e-12 * 3.09398e3
+        assert np.abs(w[:, :3] - v[:, :3]).max() <= 1e-12 * np.abs(v[:, :3]).max()
+        assert ctx.average_mass() == oracle.average_mass(pm)
+        ctx.compute_accel()
+        idx = np.arange(0, n, 997)
+        assert nbtest.rel_err(ctx.accel()[idx], oracle.forces_subset(pm, PAIRWISE, idx)).max() <= 1e-11
+    with lib.context(n, FP32) as ctx:                       # another seed gives another system; FP32 mode takes the same path
+        ctx.init_spiral(12346)
+        p2, _ = ctx.download()
+        assert np.abs(p2[:, :3] - pm[:, :3]).max() > 1.0
+
+
 def test_download_slice_on_one_gpu_is_the_whole_state(lib):
     """nb_download_slice (multi-GPU egress without the gather) on a single device: all n rows in curve order + their indices."""
     pm, v = nbtest.gen_spiral(5000, seed=4)

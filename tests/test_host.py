@@ -386,6 +386,33 @@ def test_host_checkpoint_resume(tmp_path, host, oracle):
 
 
 @pytest.mark.gpu
+def test_host_device_side_initial_conditions(tmp_path, oracle):
+    """"deviceInit": true — SPIRAL_GALAXY made on the GPU (nb_init_spiral), BENCHMARK run, final state in the snapshot file:
+    equals the CPU integrator started from the numpy restatement of the same counter-based draws."""
+    snap = str(tmp_path / "end.nbin")
+    base = json.loads(cfg_text(selected="SPIRAL_GALAXY", seed=77, years=0.08, dtYears=0.02, precision="FP64").split("\n#")[0])
+    sp = base["init"]["SPIRAL_GALAXY"]
+    sp["nStars"] = 1500
+    base["deviceInit"] = True
+    base["snapshotOut"] = snap
+    (tmp_path / "config.json").write_text(json.dumps(base))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "on the device" in r.stdout
+    raw = np.fromfile(snap, dtype=np.float64, offset=16)
+    pm1, v1 = raw[:6000].reshape(1500, 4), raw[6000:].reshape(1500, 4)
+    pm0, v0, _ = nbtest.gen_spiral_counter(1500, 77, sp["totalMass"], sp["nArms"], sp["galaxyRadius"], sp["thickness"], sp["perturbation"])
+    p_ref, v_ref = oracle.step(pm0, v0, nbtest.VV, nbtest.PAIRWISE, 0.02, 4)
+    np.testing.assert_allclose(pm1[:, :3], p_ref[:, :3], atol=1e-8)
+    np.testing.assert_allclose(v1[:, :3], v_ref[:, :3], atol=1e-8)
+    base["seed"] = None
+    del base["seed"]
+    (tmp_path / "config.json").write_text(json.dumps(base))
+    r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0 and "seed" in (r.stdout + r.stderr)
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("prec,tol", [("0", 2e-5), ("1", 1e-9)], ids=["fp32", "fp64"])
 def test_reference_system_cpp_runs_on_the_b200_library(prec, tol):
     """The reference's own System.cpp/Forces.cpp, linked with n-body-simulation_b200/host/ref_shims.cpp: System(GPU).runBenchmark goes through

@@ -177,6 +177,17 @@ def test_reference_generators_match_seeded_distributions(ref):
         ra, rb = np.linalg.norm(a[:, :3], axis=1), np.linalg.norm(b[:, :3], axis=1)
         assert abs(ra.mean() - rb.mean()) < 0.05 * rb.mean()
         assert abs(ra.max() - rb.max()) < 0.15 * rb.max()      # the reference draws from std::random_device: extremes vary run to run
+    # the counter-based restatement behind nb_init_spiral (device-side generator): same distribution again, incl. the disc
+    # geometry — thickness along the normal, radius in the plane, rotation speed v0 sqrt(r/R) around the normal
+    cp, cv, nrm = nbtest.gen_spiral_counter(4000, seed=9)
+    assert rp[:, 3] == pytest.approx(cp[:, 3])
+    for a, b in ((rp, cp), (rv, cv)):
+        ra, rb = np.linalg.norm(a[:, :3], axis=1), np.linalg.norm(b[:, :3], axis=1)
+        assert abs(ra.mean() - rb.mean()) < 0.05 * rb.mean()
+        assert abs(ra.max() - rb.max()) < 0.15 * rb.max()
+    assert np.abs(cp[:, :3] @ nrm).max() <= 6.18795e2 / 2 * (1 + 1e-12)
+    rho = np.linalg.norm(cp[:, :3] - np.outer(cp[:, :3] @ nrm, nrm), axis=1)
+    assert rho.max() <= 3.09398e3 * (1 + 1e-12) and abs(np.mean((rho / 3.09398e3) ** 2) - 0.5) < 0.03      # uniform in area
     rp, rv = ref.init_random(500)
     gp, gv = nbtest.gen_random(500, seed=9)
     assert np.abs(rp[:, :3]).max() <= 50 and np.abs(gp[:, :3]).max() <= 50
