@@ -852,7 +852,7 @@ force_near64_kernel(const float* __restrict__ pk, double* __restrict__ part, con
 // the running sum instead of 256): with the particles in curve order consecutive j pull in the same direction, the running
 // sum of a j-range is large compared with the final result, and every addition to it rounds at ITS magnitude.
 #ifndef NB_FP64_UNROLL4
-#define NB_FP64_UNROLL4 4
+#define NB_FP64_UNROLL4 8
 #endif
 #ifndef NB_FP64_UNROLL2
 #define NB_FP64_UNROLL2 4
