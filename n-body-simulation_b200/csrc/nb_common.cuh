@@ -63,7 +63,8 @@ int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 int launch_force_fp32(const float* pk, double* part, const ForceLaunch& L, int force_method, int variant, cudaStream_t st);
 int launch_force_near64(const float* pk, double* part, const ForceLaunch& L, int force_method, cudaStream_t st);
 int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, int force_method, double avg_mass, cudaStream_t st);
-int launch_potential_fp64(const double4* pos, double* pot, int it0, int nit, int ntiles, cudaStream_t st);
+int potential_splits(int nit, int sm_count);
+int launch_potential_fp64(const double4* pos, double* pot, int it0, int nit, int ntiles, long npad, int splits, cudaStream_t st);
 int force_regs_info(char* buf, int len);
 int force_i_tiles_per_cta(int variant);
 int force_fp64_i_tiles(long npad, int force_method);
@@ -82,7 +83,7 @@ int launch_pack(const StepArrays& A, long first, long count, double avg_mass, cu
 int launch_drift(const StepArrays& A, int integ, double dt, bool subtract_com, double avg_mass, cudaStream_t st);
 int launch_finish(const StepArrays& A, int integ, bool kick, double dt, int S, cudaStream_t st);
 int launch_com_final(const StepArrays& A, cudaStream_t st);
-int launch_energy_partial(const StepArrays& A, const double* pot, long first, long count, double* out4, cudaStream_t st);
+int launch_energy_partial(const StepArrays& A, const double* pot, int pot_splits, long first, long count, double* out4, cudaStream_t st);
 int launch_energy_final(const double* in4, double* out3, cudaStream_t st);
 int launch_snapshot(const double4* pos, const double4* vel, long n, double* particleData6, double* staticData2, cudaStream_t st);
 int launch_accel_export(const double* acc, long npad, long first, long count, double4* out, cudaStream_t st);

@@ -455,7 +455,7 @@ struct SnapRing {
         c = ctx;
         const size_t np = (size_t)c->npad, n = (size_t)c->n;
         auto up = [](size_t b) { return (b + 255) / 256 * 256; };
-        const size_t b_state = up(np * sizeof(double4)), b6 = up(n * 6 * sizeof(double)), b_pot = up(np * sizeof(double)),
+        const size_t b_state = up(np * sizeof(double4)), b6 = up(n * 6 * sizeof(double)), b_pot = up(4 * np * sizeof(double)),
                      b_red = up((np / kThreads) * 4 * sizeof(double)), b_out = 256;
         const size_t per_dev = 2 * b_state + b6 + b_pot + b_red + b_out, per_host = b6 + 256;
         int lo = 0, hi = 0;
@@ -497,10 +497,11 @@ struct SnapRing {
         NB_CUDA(cudaMemcpyAsync(dvel[k], c->vel, np * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
         NB_CUDA(cudaEventRecord(ready[k], c->stream));
         NB_CUDA(cudaStreamWaitEvent(stream, ready[k], 0));
-        rc = launch_potential_fp64(dpos[k], dpot[k], 0, c->ntiles, c->ntiles, stream); if (rc) return rc;
+        const int psplits = potential_splits(c->ntiles, c->sm_count);
+        rc = launch_potential_fp64(dpos[k], dpot[k], 0, c->ntiles, c->ntiles, c->npad, psplits, stream); if (rc) return rc;
         StepArrays A = arrays(c);
         A.pos = dpos[k]; A.vel = dvel[k]; A.red_part = dred[k];
-        rc = launch_energy_partial(A, dpot[k], 0, c->n, dout[k] + 4, stream); if (rc) return rc;
+        rc = launch_energy_partial(A, dpot[k], psplits, 0, c->n, dout[k] + 4, stream); if (rc) return rc;
         rc = launch_energy_final(dout[k] + 4, dout[k], stream); if (rc) return rc;
         c->launches += 5;
         NB_CUDA(cudaMemcpyAsync(h6[k], d6[k], (size_t)c->n * 6 * sizeof(double), cudaMemcpyDeviceToHost, stream));
@@ -859,11 +860,12 @@ int nb_energy(nb_ctx* c, double out[3]) {
     // Multi-GPU: collective. Every rank completes its copy of the positions, sums the pair potential of its own i-slice
     // against all j and its slice's kinetic energy, and the two sums are all-reduced (SURVEY 8e "small collectives").
     if (c->world > 1) { NB_CUDA(cudaStreamSynchronize(c->comm_stream)); rc = gather_state_all(c); if (rc) return rc; }
-    double* pot = reinterpret_cast<double*>(c->tmp4);
-    rc = launch_potential_fp64(c->pos, pot, (int)(c->i0 / kTJ), (int)(c->ni / kTJ), c->ntiles, c->stream); if (rc) return rc;
+    double* pot = reinterpret_cast<double*>(c->tmp4);                  // npad double4 = room for four partial potentials
+    const int psplits = potential_splits((int)(c->ni / kTJ), c->sm_count);
+    rc = launch_potential_fp64(c->pos, pot, (int)(c->i0 / kTJ), (int)(c->ni / kTJ), c->ntiles, c->npad, psplits, c->stream); if (rc) return rc;
     StepArrays A = arrays(c);
     long b = c->i0, e = c->i0 + c->ni; if (e > c->n) e = c->n; if (b > e) b = e;
-    rc = launch_energy_partial(A, pot, b, e - b, c->eout + 4, c->stream); if (rc) return rc;
+    rc = launch_energy_partial(A, pot, psplits, b, e - b, c->eout + 4, c->stream); if (rc) return rc;
     if (c->world > 1) NB_NCCL(nccl::AllReduce(c->eout + 4, c->eout + 4, 4, nccl::kFloat64, nccl::kSum, c->comm, c->stream));
     rc = launch_energy_final(c->eout + 4, c->eout, c->stream); if (rc) return rc;
     c->launches += 4;

@@ -945,7 +945,7 @@ constexpr int kR64 = 2;   // i-particles per thread of the potential kernel
 // E_pot = -G sum_i m_i pot[i]. The reciprocal root is the branch-free MUFU seed + second-order correction used by the force
 // kernels (12 DP operations per pair); a tile's 256 terms are summed on their own before they join the running sum.
 __global__ void __launch_bounds__(kThreads, 2)
-potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot, int it0, int ntiles) {
+potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot, int it0, int ntiles, long npad) {
     __shared__ __align__(16) double4 sm[2][kTJ];
     const int t = threadIdx.x;
     const int itile_first = it0 + blockIdx.x * kR64;
@@ -958,12 +958,15 @@ potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot,
         const double4 p = pos[(size_t)(itile_first + r) * kTJ + t];
         xi[r] = p.x; yi[r] = p.y; zi[r] = p.z; acc[r] = 0.0;
     }
+    // gridDim.y CTAs share one i-block's window (small systems: T/2 CTAs alone would leave most SMs empty); each writes its own
+    // partial potential pot[blockIdx.y][i], summed in that order by the energy reduction
+    const int kb = (int)(((long)span * blockIdx.y) / gridDim.y), ke = (int)(((long)span * (blockIdx.y + 1)) / gridDim.y);
     double4 g = make_double4(0, 0, 0, 0);
-    sm[0][t] = pos[(size_t)(itile_first % ntiles) * kTJ + t];
+    sm[kb & 1][t] = pos[(size_t)((itile_first + kb) % ntiles) * kTJ + t];
     __syncthreads();
-    for (int k = 0; k < span; ++k) {
+    for (int k = kb; k < ke; ++k) {
         const int b = k & 1;
-        const bool more = (k + 1 < span);
+        const bool more = (k + 1 < ke);
         if (more) g = pos[(size_t)((itile_first + k + 1) % ntiles) * kTJ + t];
         double w[kR64];
         bool any = false;
@@ -1000,7 +1003,7 @@ potential_fp64_kernel(const double4* __restrict__ pos, double* __restrict__ pot,
         __syncthreads();
     }
 #pragma unroll
-    for (int r = 0; r < kR64; ++r) pot[(size_t)(itile_first + r) * kTJ + t] = acc[r];
+    for (int r = 0; r < kR64; ++r) pot[(size_t)blockIdx.y * npad + (size_t)(itile_first + r) * kTJ + t] = acc[r];
 }
 
 template <typename K>
@@ -1094,11 +1097,18 @@ int launch_force_fp64(const double4* pos, double* part, const ForceLaunch& L, in
                                            : launch_force_fp64_r<2>(pos, part, L, force_method, avg_mass, st);
 }
 
-int launch_potential_fp64(const double4* pos, double* pot, int it0, int nit, int ntiles, cudaStream_t st) {
+// Number of partial potentials per particle launch_potential_fp64 writes (pot must hold that many arrays of npad doubles, <= 4)
+int potential_splits(int nit, int sm_count) {
+    const int blocks = nit / kR64;
+    int S = (4 * sm_count + blocks - 1) / (blocks > 0 ? blocks : 1);
+    return S < 1 ? 1 : (S > 4 ? 4 : S);
+}
+
+int launch_potential_fp64(const double4* pos, double* pot, int it0, int nit, int ntiles, long npad, int splits, cudaStream_t st) {
     if (nit <= 0) return NB_OK;
     if (nit % kR64) return fail(NB_ERR_INVALID, "potential: i-tile count %d not a multiple of %d", nit, kR64);
-    dim3 grid((unsigned)(nit / kR64)), block(kThreads);
-    potential_fp64_kernel<<<grid, block, 0, st>>>(pos, pot, it0, ntiles);
+    dim3 grid((unsigned)(nit / kR64), (unsigned)(splits < 1 ? 1 : splits)), block(kThreads);
+    potential_fp64_kernel<<<grid, block, 0, st>>>(pos, pot, it0, ntiles, npad);
     NB_CUDA(cudaGetLastError());
     return NB_OK;
 }

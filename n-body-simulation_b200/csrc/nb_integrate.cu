@@ -172,7 +172,7 @@ reduce4_kernel(const double* __restrict__ red_part, long nblocks, double* __rest
 // Energy: block sums of (kinetic, m_i * pot_i, -, -) over all particles.
 __global__ void __launch_bounds__(kThreads)
 energy_partial_kernel(const double4* __restrict__ pos, const double4* __restrict__ vel, const double* __restrict__ pot,
-                      long first, long count, double* __restrict__ red_part) {
+                      int pot_splits, long npad, long first, long count, double* __restrict__ red_part) {
     __shared__ double sh[32];
     const long k = (long)blockIdx.x * kThreads + threadIdx.x;
     double r[4] = {0.0, 0.0, 0.0, 0.0};
@@ -180,7 +180,9 @@ energy_partial_kernel(const double4* __restrict__ pos, const double4* __restrict
         const long i = first + k;
         const double4 p = pos[i], v = vel[i];
         r[0] = 0.5 * p.w * (v.x * v.x + v.y * v.y + v.z * v.z);   // core/System.cpp:66-70
-        r[1] = p.w * pot[i];
+        double phi = 0.0;
+        for (int s = 0; s < pot_splits; ++s) phi += pot[(size_t)s * npad + i];      // partial potentials in split order
+        r[1] = p.w * phi;
     }
     block_sum4(r, sh);
     if (threadIdx.x == 0) { double* o = red_part + (size_t)blockIdx.x * 4; o[0] = r[0]; o[1] = r[1]; o[2] = 0.0; o[3] = 0.0; }
@@ -279,10 +281,10 @@ int launch_com_final(const StepArrays& A, cudaStream_t st) {
 
 // Kinetic and potential sums over the particles [first, first+count) -> out4 = (sum 1/2 m v^2, sum m_i pot_i, 0, 0).
 // A rank of a multi-GPU run sums its own slice; the four doubles are then all-reduced before launch_energy_final.
-int launch_energy_partial(const StepArrays& A, const double* pot, long first, long count, double* out4, cudaStream_t st) {
+int launch_energy_partial(const StepArrays& A, const double* pot, int pot_splits, long first, long count, double* out4, cudaStream_t st) {
     const long nb = count > 0 ? (long)blocks_for(count) : 0;
     if (nb > 0) {
-        energy_partial_kernel<<<(unsigned)nb, kThreads, 0, st>>>(A.pos, A.vel, pot, first, count, A.red_part);
+        energy_partial_kernel<<<(unsigned)nb, kThreads, 0, st>>>(A.pos, A.vel, pot, pot_splits, A.npad, first, count, A.red_part);
         NB_CUDA(cudaGetLastError());
     }
     reduce4_kernel<<<1, 1024, 0, st>>>(A.red_part, nb, out4);
