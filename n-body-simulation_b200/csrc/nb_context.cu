@@ -691,12 +691,16 @@ int nb_comm_init(nb_ctx* c, const void* id128, int rank, int world) {
     // NCCL connects its peers lazily, inside the first collective of each kind — seconds of host-side set-up that would
     // otherwise land in the first step (measured at N = 16M on two GPUs: the rank that ran it waited 5.7 s of a 53 s step for its
     // remote slices). Run one tiny all-gather and all-reduce now, on the streams the step uses, while nothing else is queued.
-    double* scratch = reinterpret_cast<double*>(c->pos);            // not uploaded yet (checked above): free to use
-    NB_NCCL(nccl::AllGather(scratch + rank, scratch, 1, nccl::kFloat64, c->comm, c->comm_stream));
+    // The all-gather is the step's own (same buffer, same size: NCCL picks protocol and channel count by size, and a small
+    // message would leave the large-message path unconnected — at N = 16M on four GPUs one rank still lost 1.4 s of its first step
+    // after a one-element warm-up); the arrays hold nothing yet (no upload so far, checked above).
+    if (c->precision == NB_PREC_FP32)
+        NB_NCCL(nccl::AllGather(c->pk + (size_t)c->i0 * kNC, c->pk, (size_t)c->ni * kNC, nccl::kFloat32, c->comm, c->comm_stream));
+    else
+        NB_NCCL(nccl::AllGather((const double*)(c->pos + c->i0), (double*)c->pos, (size_t)c->ni * 4, nccl::kFloat64, c->comm, c->comm_stream));
     NB_NCCL(nccl::AllReduce(c->red, c->red, 4, nccl::kFloat64, nccl::kSum, c->comm, c->stream));
     NB_CUDA(cudaStreamSynchronize(c->comm_stream));
     NB_CUDA(cudaStreamSynchronize(c->stream));
-    NB_CUDA(cudaMemsetAsync(c->pos, 0, (size_t)world * sizeof(double), c->stream));
     NB_CUDA(cudaMemsetAsync(c->red, 0, 16 * sizeof(double), c->stream));
     return NB_OK;
 }
