@@ -3,19 +3,21 @@
 // Replaces calculatePairwiseForceKernel / calculateAdaptiveForcesKernel (reference cuda/ForceKernels.cu:14-96,99-170)
 // with the semantics of the CPU oracle (core/Forces.cpp:98-179,301-387): a_i = sum_{j != i, r^2 >= 1e-10} G m_j d / s^3.
 //
-// FP32 mode (force_fp32_kernel)
-//   * packed FP32x2 arithmetic (FADD2/FMUL2/FFMA2, new on sm_100): one instruction works on TWO j-particles, so the
-//     9+12 FP32 operations of an interaction cost ~10 issue slots instead of 21 and the MUFU/LDS/select instructions
-//     issue in the slots that frees;
-//   * two-float (hi+lo) positions: d = (xjh - xih) + (xjl - xil) keeps the relative error of d at ~1e-7 for any
-//     separation (plain FP32 coordinates lose close pairs: error ~ eps*|x|/|d|);
-//   * R i-particles per thread held in registers (duplicated into both halves of a register pair), j-tiles of 256
-//     particles staged in shared memory either with plain loads (variant 1) or with cp.async.bulk + mbarrier
-//     (variant 2, UBLKCP in SASS) into a 4-deep ring;
-//   * FP32 accumulation over 128 j-particles (64 per half), then flushed into FP64 accumulators;
-//   * j-range split over gridDim.y so that small N still fills 148 SMs; partial sums go to part[s][3][npad] and are
-//     reduced in fixed order by the integrator kernel (deterministic, no atomics).
-// FP64 mode (force_fp64_kernel): same tiling with double4 tiles and DFMA arithmetic.
+// FP32 mode, production path (variant 3) = two kernels per evaluation:
+//   * force_fp32_r4_kernel — FP32 far field: j-tiles of 256 particles arrive by cp.async.bulk into a 3-stage ring (mbarrier per
+//     stage, UBLKCP / SYNCS in SASS) from this GPU's own packed-tile array; every tile is re-expressed relative to the CTA's
+//     origin (or, close to the CTA, per warp and 64-particle sub-tile relative to the warp's origin) so that one float per
+//     coordinate carries the separation; packed FP32x2 arithmetic (FFMA2 / FMUL2: one instruction = two j-particles), four
+//     i-particles per thread, mass-scaled frame (11 packed operations + 1 MUFU.RSQ per interaction); FP32 partial sums are
+//     flushed every 128 j into FP64 sums;
+//   * force_near64_kernel — FP64 near field: the (warp, sub-tile) pairs the far kernel's box tests leave out (self pairs,
+//     pairs under the cut-off, close encounters) on the two-float positions, one owner (128 i-particles) per CTA.
+//   Variants 1 (force_fp32_ld_kernel: global two-float coordinates, plain loads; also behind nb_force_noalloc) and 2
+//   (force_fp32_tma_kernel: CTA frame, FP32 two-float near field in one kernel) are kept as cross-checks.
+// FP64 mode (force_fp64_kernel): tiles of (x, y, z, G m) doubles, 4 (PAIRWISE) or 2 (ADAPTIVE) i-particles per thread, branch-free
+//   G m s^-3 from the MUFU.RSQ64H seed; potential_fp64_kernel: the pair potential of nb_energy, every unordered pair once.
+// The j-range of every launch is split over gridDim.y; partial sums go to part[s][3][npad] and are reduced in slot order by the
+// integrator kernel (deterministic, no atomics).
 #include "nb_common.cuh"
 
 #include <mutex>
