@@ -217,6 +217,16 @@ def test_csv_sink_is_byte_identical_to_the_reference_writer(host, ref, tmp_path)
     assert ta == tb
 
 
+def test_device_init_key_is_validated_before_any_device_is_touched(tmp_path):
+    """"deviceInit": true is for SPIRAL_GALAXY + BENCHMARK + a seed; anything else is a configuration error (no GPU needed to say so)."""
+    for over in (dict(selected="RANDOM", seed=1), dict(selected="SPIRAL_GALAXY"), dict(selected="SPIRAL_GALAXY", seed=1, outputMode="FILE_CSV")):
+        c = json.loads(cfg_text(**over).split("\n#")[0])
+        c["deviceInit"] = True
+        (tmp_path / "config.json").write_text(json.dumps(c))
+        r = subprocess.run([HOST_BIN], cwd=tmp_path, capture_output=True, text=True, timeout=120)
+        assert r.returncode == 1 and "deviceInit" in r.stderr, r.stderr
+
+
 def test_host_binary_fails_loudly_without_gpu(tmp_path, lib):
     if lib.l.nb_device_count() > 0:
         pytest.skip("a GPU is present")
